@@ -1,0 +1,460 @@
+/*
+ * pathtrace.cu -- sm_100a kernels behind librtcuda.so.
+ *
+ *   rt_prep_scene     one block: turns the buffers the host uploaded (shaderTypes.h
+ *                     layout, AoS) into the prepared scene of rt_scene_layout.h
+ *   pathTrace_*       the per-pixel path tracer; replaces the Metal kernel
+ *                     `pathTrace`, reference RTrace/raytrace.metal:11-111 with
+ *                     RTrace/sampling.metal:16-26,39-66,97-157,198-236
+ *   rt_resolve_rgba8  RTrace/image.swift:40-65 tone map as a device pass
+ *   rt_debug_eval     evaluates single device functions for bit-compare tests
+ *
+ * Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -prec-div=true
+ *        -prec-sqrt=true -ftz=false -lineinfo  (see rt_device_math.cuh for why).
+ *
+ * Kernel shape (DESIGN.md has the numbers): one thread per pixel, a warp covers an
+ * 8x4 pixel tile, a block 16x8 pixels.  Each block first stages the prepared scene
+ * from HBM into shared memory; per sample the thread walks the bounce loop with the
+ * Halton dimension fixed at compile time (the bounce loop is unrolled), and every
+ * ray query is a loop over ALL primitives: there is no acceleration structure.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rtcuda.h"
+#include "rt_scene_layout.h"
+#include "rt_device_math.cuh"
+
+using namespace rt;
+
+/* constant-bank copy of the intersection section (variant "const"): every lane
+ * reads the same triangle, so the operands come through the uniform datapath and
+ * cost neither LSU issue slots nor vector registers. */
+#define RT_CONST_TRIS 1024
+#define RT_CONST_SPHERES 1024
+__constant__ float4 c_isect[3 * RT_CONST_TRIS];
+__constant__ float4 c_sphere[RT_CONST_SPHERES];
+
+/* ------------------------------------------------------------------ prep ---- */
+struct SimdF3 { float x, y, z, pad; };
+
+extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camera,
+                                         const unsigned char *__restrict__ materials,
+                                         const unsigned char *__restrict__ lights,
+                                         const unsigned char *__restrict__ vertices,
+                                         const unsigned char *__restrict__ spheres,
+                                         float *__restrict__ scene, RTSceneLayout lay) {
+    const int tid = threadIdx.x, nth = blockDim.x;
+    if (tid == 0) {
+        /* generateCameraRay's per-launch part, sampling.metal:131-139 */
+        const float *cam = (const float *)camera;
+        const int *cami = (const int *)camera;
+        f3 position = mk(cam[0], cam[1], cam[2]);
+        f3 direction = mk(cam[4], cam[5], cam[6]);
+        f3 up = mk(cam[8], cam[9], cam[10]);
+        int resx = cami[12], resy = cami[13];
+        float fov = cam[14], ev100 = cam[15];
+        float aspectRatio = (float)(resy != 0 ? resx / resy : 0);   /* integer division, :132 */
+        float halfWidth = tan_det(fov / 2.0f);
+        float halfHeight = halfWidth / aspectRatio;
+        f3 w = -normalize(direction);
+        f3 u = normalize(cross(up, w));
+        f3 v = normalize(cross(w, u));
+        scene[RT_HDR_CAM_O + 0] = position.x; scene[RT_HDR_CAM_O + 1] = position.y; scene[RT_HDR_CAM_O + 2] = position.z;
+        scene[RT_HDR_CAM_U + 0] = u.x; scene[RT_HDR_CAM_U + 1] = u.y; scene[RT_HDR_CAM_U + 2] = u.z;
+        scene[RT_HDR_CAM_V + 0] = v.x; scene[RT_HDR_CAM_V + 1] = v.y; scene[RT_HDR_CAM_V + 2] = v.z;
+        scene[RT_HDR_CAM_W + 0] = w.x; scene[RT_HDR_CAM_W + 1] = w.y; scene[RT_HDR_CAM_W + 2] = w.z;
+        scene[RT_HDR_HALF_W] = halfWidth;
+        scene[RT_HDR_HALF_H] = halfHeight;
+        scene[RT_HDR_RES_X] = (float)resx;
+        scene[RT_HDR_RES_Y] = (float)resy;
+        scene[RT_HDR_EXPOSURE] = ev100;   /* mode B fills the real value */
+        for (int i = RT_HDR_EXPOSURE + 1; i < RT_HDR_WORDS; i++) scene[i] = 0.0f;
+    }
+    for (uint32_t i = tid; i < lay.Tp; i += nth) {
+        float *is = scene + lay.isect + RT_ISECT_WORDS * i;
+        float *sh = scene + lay.shade + i;
+        if (i < lay.T) {
+            const SimdF3 *vv = (const SimdF3 *)vertices + 3 * i;
+            f3 v0 = mk(vv[0].x, vv[0].y, vv[0].z);
+            f3 v1 = mk(vv[1].x, vv[1].y, vv[1].z);
+            f3 v2 = mk(vv[2].x, vv[2].y, vv[2].z);
+            f3 e1 = v1 - v0, e2 = v2 - v0;
+            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = e1.x;
+            is[4] = e1.y; is[5] = e1.z; is[6] = e2.x; is[7] = e2.y;
+            is[8] = e2.z; is[9] = 0.0f; is[10] = 0.0f; is[11] = 0.0f;
+            f3 n = normalize(cross(e1, e2));                                 /* sampling.metal:16-26 */
+            f3 right = normalize(cross(n, mk(0.0072f, 1.0f, 0.0034f)));      /* sampling.metal:57   */
+            f3 fwd = cross(right, n);                                        /* sampling.metal:61   */
+            const float *m = (const float *)(materials + 48 * (size_t)i);
+            f3 em = mk(m[8], m[9], m[10]);
+            sh[(RT_SH_NX + 0) * lay.Tp] = n.x; sh[(RT_SH_NX + 1) * lay.Tp] = n.y; sh[(RT_SH_NX + 2) * lay.Tp] = n.z;
+            sh[(RT_SH_RX + 0) * lay.Tp] = right.x; sh[(RT_SH_RX + 1) * lay.Tp] = right.y; sh[(RT_SH_RX + 2) * lay.Tp] = right.z;
+            sh[(RT_SH_FX + 0) * lay.Tp] = fwd.x; sh[(RT_SH_FX + 1) * lay.Tp] = fwd.y; sh[(RT_SH_FX + 2) * lay.Tp] = fwd.z;
+            sh[(RT_SH_DR + 0) * lay.Tp] = m[0]; sh[(RT_SH_DR + 1) * lay.Tp] = m[1]; sh[(RT_SH_DR + 2) * lay.Tp] = m[2];
+            sh[(RT_SH_ER + 0) * lay.Tp] = em.x; sh[(RT_SH_ER + 1) * lay.Tp] = em.y; sh[(RT_SH_ER + 2) * lay.Tp] = em.z;
+            sh[RT_SH_FLAG * lay.Tp] = (length(em) > 0.0f) ? 1.0f : 0.0f;     /* raytrace.metal:57   */
+            sh[RT_SH_METAL * lay.Tp] = m[4];
+            sh[RT_SH_ROUGH * lay.Tp] = m[5];
+        } else {
+            /* padding triangles are degenerate (all zero): det == 0, never accepted */
+            for (int k = 0; k < RT_ISECT_WORDS; k++) is[k] = 0.0f;
+            for (int k = 0; k < RT_SHADE_ROWS; k++) sh[k * lay.Tp] = 0.0f;
+        }
+    }
+    for (uint32_t j = tid; j < lay.Sp; j += nth) {
+        float *sp = scene + lay.sphere + 4 * j;
+        float *sh = scene + lay.sshade + j;
+        if (j < lay.S) {
+            const float *s = (const float *)(spheres + 80 * (size_t)j);   /* SphereGPU: center@0 material@16 radius@64 */
+            sp[0] = s[0]; sp[1] = s[1]; sp[2] = s[2]; sp[3] = s[16];
+            f3 em = mk(s[12], s[13], s[14]);
+            sh[(RT_SSH_DR + 0) * lay.Sp] = s[4]; sh[(RT_SSH_DR + 1) * lay.Sp] = s[5]; sh[(RT_SSH_DR + 2) * lay.Sp] = s[6];
+            sh[(RT_SSH_ER + 0) * lay.Sp] = em.x; sh[(RT_SSH_ER + 1) * lay.Sp] = em.y; sh[(RT_SSH_ER + 2) * lay.Sp] = em.z;
+            sh[RT_SSH_FLAG * lay.Sp] = (length(em) > 0.0f) ? 1.0f : 0.0f;
+        } else {
+            /* padding sphere: radius 0 far away; C > 0 and disc < 0 for any finite ray */
+            sp[0] = 0.0f; sp[1] = 3.0e18f; sp[2] = 0.0f; sp[3] = 0.0f;
+            for (int k = 0; k < RT_SSHADE_ROWS; k++) sh[k * lay.Sp] = 0.0f;
+        }
+    }
+    for (uint32_t l = tid; l < lay.L; l += nth) {
+        const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
+        float *d = scene + lay.light + RT_LIGHT_WORDS * l;
+        d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = 0.0f;
+        d[4] = s[4]; d[5] = s[5]; d[6] = s[6]; d[7] = 0.0f;
+    }
+}
+
+/* ------------------------------------------------------------- intersector ---- */
+/*
+ * Division-free Moller-Trumbore in the scaled form fixed by the arithmetic
+ * contract: with p = cross(d,e2), det = dot(e1,p), tv = o - v0,
+ * U = dot(tv,p), q = cross(tv,e1), V = dot(d,q), N = dot(e2,q), everything
+ * multiplied by sign(det) and a = |det|, a hit needs
+ *     U >= 0, V >= 0, U + V <= a, N >= tmin*a, N*bestD < bestN*a.
+ * (bestN,bestD) starts at (tmax,1).  One division, bestN/bestD, after the loop.
+ */
+struct Best { float N, D; uint32_t id; };
+
+__device__ __forceinline__ bool tri_test(float4 A, float4 B, float4 C, f3 o, f3 d, float tmin,
+                                         float bestN, float bestD, float &N_out, float &a_out) {
+    f3 v0 = mk(A.x, A.y, A.z), e1 = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x);
+    f3 p = cross(d, e2);
+    float det = dot(e1, p);
+    f3 tv = o - v0;
+    float U = dot(tv, p);
+    f3 q = cross(tv, e1);
+    float V = dot(d, q);
+    float N = dot(e2, q);
+    uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    U = __uint_as_float(__float_as_uint(U) ^ sgn);
+    V = __uint_as_float(__float_as_uint(V) ^ sgn);
+    N = __uint_as_float(__float_as_uint(N) ^ sgn);
+    float a = fabsf(det);
+    N_out = N; a_out = a;
+    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & (N >= tmin * a) & (N * bestD < bestN * a);
+}
+
+/* sphere: m = o - c, A = d.d, B = m.d, C = m.m - r*r, disc = B*B - A*C, roots
+ * (-B -+ sqrt(disc)) / A, nearer root first (rt_detmath.h: rt_sphere_test). */
+__device__ __forceinline__ bool sphere_test(float4 S, f3 o, f3 d, float tmin,
+                                            float bestN, float bestD, float &N_out, float &a_out) {
+    f3 m = o - mk(S.x, S.y, S.z);
+    float A = dot(d, d);
+    float B = dot(m, d);
+    float C = fmaf(-S.w, S.w, dot(m, m));
+    float disc = fmaf(B, B, -(A * C));
+    float sq = sqrtf(fmaxf(disc, 0.0f));
+    bool real = disc >= 0.0f;
+    float N0 = -B - sq, N1 = -B + sq;
+    bool ok0 = real & (N0 >= tmin * A) & (N0 * bestD < bestN * A);
+    bool ok1 = real & (N1 >= tmin * A) & (N1 * bestD < bestN * A);
+    N_out = ok0 ? N0 : N1; a_out = A;
+    return ok0 | ok1;
+}
+
+template <bool CONST_BANK>
+struct SceneRef {
+    const float4 *tri;      /* shared memory (or unused) */
+    const float4 *sph;
+    uint32_t T, S;
+    __device__ __forceinline__ float4 triA(uint32_t i, int k) const { return CONST_BANK ? c_isect[3 * i + k] : tri[3 * i + k]; }
+    __device__ __forceinline__ float4 sphere(uint32_t j) const { return CONST_BANK ? c_sphere[j] : sph[j]; }
+};
+
+template <bool CONST_BANK>
+__device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax,
+                                            float &dist, uint32_t &id) {
+    float bestN = tmax, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+#pragma unroll 4
+    for (uint32_t i = 0; i < sc.T; i++) {
+        float N, a;
+        if (tri_test(sc.triA(i, 0), sc.triA(i, 1), sc.triA(i, 2), o, d, tmin, bestN, bestD, N, a)) {
+            bestN = N; bestD = a; best = i;
+        }
+    }
+#pragma unroll 2
+    for (uint32_t j = 0; j < sc.S; j++) {
+        float N, a;
+        if (sphere_test(sc.sphere(j), o, d, tmin, bestN, bestD, N, a)) {
+            bestN = N; bestD = a; best = sc.T + j;
+        }
+    }
+    id = best;
+    dist = bestN / bestD;
+    return best != 0xffffffffu;
+}
+
+template <bool CONST_BANK>
+__device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax) {
+    bool hit = false;
+#pragma unroll 4
+    for (uint32_t i = 0; i < sc.T; i++) {
+        float N, a;
+        hit |= tri_test(sc.triA(i, 0), sc.triA(i, 1), sc.triA(i, 2), o, d, tmin, tmax, 1.0f, N, a);
+    }
+#pragma unroll 2
+    for (uint32_t j = 0; j < sc.S; j++) {
+        float N, a;
+        hit |= sphere_test(sc.sphere(j), o, d, tmin, tmax, 1.0f, N, a);
+    }
+    return hit;
+}
+
+/* ---------------------------------------------------------------- shading ---- */
+/* sampling.metal:198-236 with the literals of :207-209 folded:
+ * samplePosition = center + (0.25,0,0)*ux + (0,0,0.25)*uy.  The products with the
+ * zero components are +-0 and drop out exactly, so only x and z move. */
+__device__ __forceinline__ f3 sample_area_light(f3 center, f3 lcolor, float ux, float uy, f3 P,
+                                                f3 &ldir, float &ldist) {
+    ux = ux * 2.0f - 1.0f;
+    uy = uy * 2.0f - 1.0f;
+    f3 samplePosition = mk(center.x + 0.25f * ux, center.y, center.z + 0.25f * uy);
+    f3 ld = samplePosition - P;
+    float dist = length(ld);
+    float inv = 1.0f / fmaxf(dist, 1e-3f);
+    ld = ld * inv;
+    f3 c = lcolor * (inv * inv);
+    /* dot(-ld, (0,-1,0)) = fma(-z,0, fma(-y,-1, -x*0)) = ld.y (the zero terms are exact) */
+    c = c * saturate(ld.y);
+    ldir = ld; ldist = dist;
+    return c;
+}
+
+/* sampling.metal:39-49 */
+__device__ __forceinline__ f3 sample_cosine_hemisphere(float ux, float uy) {
+    float phi = 6.2831854820251465f * ux;          /* (2.0f * M_PI_F) * u.x */
+    float sp, cp;
+    sincos_det(phi, sp, cp);
+    float ct = sqrtf(uy);
+    float st = sqrtf(1.0f - ct * ct);
+    return mk(st * cp, ct, st * sp);
+}
+
+/* -------------------------------------------------------------- the kernel ---- */
+#define RT_BLOCK_W 16
+#define RT_BLOCK_H 8
+#define RT_BLOCK_THREADS 128
+
+template <bool CONST_BANK, int MAXB>
+__device__ __forceinline__ f3 trace_path(const SceneRef<CONST_BANK> &sc, const float *__restrict__ sm,
+                                         const RTSceneLayout &lay, int bounces, uint32_t numLights,
+                                         uint32_t px, uint32_t py, uint32_t i);
+
+template <int B>
+struct HaltonDims {
+    __device__ static __forceinline__ void light(uint32_t i, float &a, float &b) { a = halton<2 + 5 * B>(i); b = halton<3 + 5 * B>(i); }
+    __device__ static __forceinline__ void bsdf(uint32_t i, float &a, float &b) { a = halton<4 + 5 * B>(i); b = halton<5 + 5 * B>(i); }
+};
+
+/* one bounce of raytrace.metal:47-101; returns false when the path ends */
+template <bool CONST_BANK, int B>
+__device__ __forceinline__ bool bounce_step(const SceneRef<CONST_BANK> &sc, const float *__restrict__ sm,
+                                            const RTSceneLayout &lay, uint32_t numLights, uint32_t i,
+                                            f3 &ro, f3 &rd, f3 &color, f3 &acc) {
+    float dist; uint32_t id;
+    if (!closest_hit<CONST_BANK>(sc, ro, rd, 0.001f, 1000.0f, dist, id)) return false;     /* :51-53 */
+
+    f3 normal, right, fwd, diffuse;
+    if (id < lay.T) {
+        const float *sh = sm + lay.shade + id;
+        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                              /* :57-60 */
+            acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
+            return false;
+        }
+        normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+        right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
+        fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
+        diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
+    } else {
+        uint32_t j = id - lay.T;
+        const float *sh = sm + lay.sshade + j;
+        if (sh[RT_SSH_FLAG * lay.Sp] != 0.0f) {
+            acc = mk(sh[(RT_SSH_ER + 0) * lay.Sp], sh[(RT_SSH_ER + 1) * lay.Sp], sh[(RT_SSH_ER + 2) * lay.Sp]);
+            return false;
+        }
+        float4 S = sc.sphere(j);
+        f3 hp = ro + rd * dist;
+        normal = normalize(hp - mk(S.x, S.y, S.z));
+        right = normalize(cross(normal, mk(0.0072f, 1.0f, 0.0034f)));
+        fwd = cross(right, normal);
+        diffuse = mk(sh[(RT_SSH_DR + 0) * lay.Sp], sh[(RT_SSH_DR + 1) * lay.Sp], sh[(RT_SSH_DR + 2) * lay.Sp]);
+    }
+    f3 P = (ro + rd * dist) + normal * 1e-3f;                                               /* :67 */
+
+    float wx, wy;
+    HaltonDims<B>::light(i, wx, wy);                                                        /* :72-73 */
+    color = color * diffuse;                                                                /* :76 */
+    for (uint32_t l = 0; l < numLights; l++) {
+        const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
+        f3 ldir; float ldist;
+        f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+        lightColor = lightColor * saturate(dot(normal, ldir));                              /* :75 */
+        /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
+        if (!any_hit<CONST_BANK>(sc, P, ldir, 0.0f, ldist - 1e-3f))
+            acc = acc + lightColor * color;                                                 /* :88 */
+    }
+    float ux, uy;
+    HaltonDims<B>::bsdf(i, ux, uy);                                                         /* :93-94 */
+    f3 s = sample_cosine_hemisphere(ux, uy);
+    f3 sd = (right * s.x + normal * s.y) + fwd * s.z;                                       /* sampling.metal:65 */
+    ro = P;                                                                                 /* :99-100 */
+    rd = sd;
+    return true;
+}
+
+template <bool CONST_BANK>
+__device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
+                                               float4 *__restrict__ out, const RTLaunchParams p,
+                                               const RTSceneLayout lay, float *sm) {
+    /* stage the prepared scene HBM -> shared memory (coalesced 128-bit copies) */
+    {
+        const float4 *src = (const float4 *)scene;
+        float4 *dst = (float4 *)sm;
+        const uint32_t n4 = lay.words >> 2;
+        for (uint32_t k = threadIdx.x; k < n4; k += RT_BLOCK_THREADS) dst[k] = src[k];
+    }
+    __syncthreads();
+
+    /* warp = 8x4 pixels, block = 2x2 warps = 16x8 pixels */
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t x = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8 + (lane & 7);
+    const uint32_t ly = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4 + (lane >> 3);
+    if (x >= (uint32_t)p.width || ly >= (uint32_t)p.rows) return;
+    const uint32_t y = (uint32_t)p.row0 + ly;
+    const size_t pix = (size_t)ly * (uint32_t)p.width + x;
+
+    SceneRef<CONST_BANK> sc;
+    sc.tri = (const float4 *)(sm + lay.isect);
+    sc.sph = (const float4 *)(sm + lay.sphere);
+    sc.T = lay.T; sc.S = lay.S;
+
+    const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
+    const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);
+    const f3 cam_v = mk(sm[RT_HDR_CAM_V], sm[RT_HDR_CAM_V + 1], sm[RT_HDR_CAM_V + 2]);
+    const f3 cam_w = mk(sm[RT_HDR_CAM_W], sm[RT_HDR_CAM_W + 1], sm[RT_HDR_CAM_W + 2]);
+    const float halfW = sm[RT_HDR_HALF_W], halfH = sm[RT_HDR_HALF_H];
+    const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
+    const float fx = (float)(int)x, fy = (float)(int)y;
+
+    const uint32_t offset = offsets[pix];                               /* raytrace.metal:37, hoisted */
+    f3 lum = mk(0.0f, 0.0f, 0.0f);
+    if (p.accumulate) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
+
+    for (uint32_t k = 0; k < p.spp; k++) {
+        const uint32_t i = offset + (p.firstSample + k);
+        /* camera ray, sampling.metal:141-147 */
+        float jx = halton<0>(i), jy = halton<1>(i);
+        float s = ((fx + jx) / resX) * 2.0f - 1.0f;
+        float t = -(((fy + jy) / resY) * 2.0f - 1.0f);
+        f3 rd = normalize((cam_u * (s * halfW) + cam_v * (t * halfH)) - cam_w);
+        f3 ro = cam_o;
+
+        f3 acc = mk(0.0f, 0.0f, 0.0f);
+        f3 color = mk(1.0f, 1.0f, 1.0f);
+        const int nb = p.bounces;
+        do {
+            if (!bounce_step<CONST_BANK, 0>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 2) break;
+            if (!bounce_step<CONST_BANK, 1>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 3) break;
+            if (!bounce_step<CONST_BANK, 2>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 4) break;
+            bounce_step<CONST_BANK, 3>(sc, sm, lay, p.numLights, i, ro, rd, color, acc);
+        } while (0);
+        lum = lum + acc;                                                /* raytrace.metal:103 */
+    }
+
+    float4 o;
+    if (p.accumulate) {
+        o = make_float4(lum.x, lum.y, lum.z, (float)(p.firstSample + p.spp));
+    } else {
+        float samples = (float)p.spp;                                   /* raytrace.metal:106-109 */
+        o = make_float4(lum.x / samples, lum.y / samples, lum.z / samples, 1.0f);
+    }
+    out[pix] = o;
+}
+
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_smem(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+               const RTLaunchParams p, const RTSceneLayout lay) {
+    extern __shared__ __align__(16) float sm[];
+    pathtrace_body<false>(scene, offsets, out, p, lay, sm);
+}
+
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_const(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+                const RTLaunchParams p, const RTSceneLayout lay) {
+    extern __shared__ __align__(16) float sm[];
+    pathtrace_body<true>(scene, offsets, out, p, lay, sm);
+}
+
+/* ----------------------------------------------------------------- resolve ---- */
+/* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.
+ * powf here is CUDA's (<= 2 ulp); the result is compared with +-1 LSB. */
+extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar4 *__restrict__ out,
+                                            unsigned long long n, int divideByAlpha) {
+    unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = in[i];
+    float c[3] = { v.x, v.y, v.z };
+    unsigned char r[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float value = c[k];
+        if (divideByAlpha) value = value / v.w;
+        value *= 2.0f;
+        value = value / (value + 1.0f);
+        value = powf(value, 1.0f / 2.2f);
+        value = fmaxf(0.0f, fminf(1.0f, value));
+        r[k] = (unsigned char)(value * 255.0f);
+    }
+    out[i] = make_uchar4(r[0], r[1], r[2], 255);
+}
+
+/* ------------------------------------------------------------------- debug ---- */
+/* what: 0 halton(i,d) [in: u32 pairs]          -> float  (compile-time-base path)
+ *       1 sincos(x)   [in: float]              -> float2
+ *       2 hash(x)     [in: u32]                -> u32
+ *       3 halton_rt(i,d)                       -> float  (generic loop)            */
+template <int D>
+__device__ float halton_dispatch(uint32_t i, uint32_t d) {
+    if (d == D) return halton<D>(i);
+    if constexpr (D < 23) return halton_dispatch<D + 1>(i, d); else return 0.0f;
+}
+
+extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, void *__restrict__ out, uint32_t n) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    if (what == 0) {
+        const uint32_t *p = (const uint32_t *)in;
+        ((float *)out)[k] = halton_dispatch<0>(p[2 * k], p[2 * k + 1]);
+    } else if (what == 1) {
+        float s, c;
+        sincos_det(((const float *)in)[k], s, c);
+        ((float *)out)[2 * k] = s; ((float *)out)[2 * k + 1] = c;
+    } else if (what == 2) {
+        ((uint32_t *)out)[k] = hash_u32(((const uint32_t *)in)[k]);
+    } else if (what == 3) {
+        const uint32_t *p = (const uint32_t *)in;
+        ((float *)out)[k] = halton_rt(p[2 * k], p[2 * k + 1]);
+    }
+}

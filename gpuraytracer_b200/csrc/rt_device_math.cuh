@@ -1,0 +1,135 @@
+/*
+ * rt_device_math.cuh -- device-side arithmetic of the path-tracing kernels.
+ *
+ * The translation unit is compiled with --fmad=false, IEEE division and square
+ * root and no flush-to-zero, so that
+ *   - a * b + c written in the kernels is two roundings (the reference's shader
+ *     expressions, RTrace/raytrace.metal and RTrace/sampling.metal, evaluated
+ *     operator by operator), and
+ *   - a fused multiply-add happens exactly where fmaf() is written: inside the
+ *     functions that stand in for the Metal standard library and the Metal
+ *     ray/triangle query (both closed source; definitions in DESIGN.md section
+ *     "Arithmetic contract").
+ * With that, per-pixel results do not depend on how the kernel schedules the
+ * work, and discrete outcomes (hit / miss, shadowed / lit) cannot flip.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rt {
+
+struct f3 { float x, y, z; };
+
+__device__ __forceinline__ f3 mk(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ f3 operator-(f3 a) { return mk(-a.x, -a.y, -a.z); }
+
+/* ---- Metal stdlib stand-ins (fused where written) ---------------------------- */
+__device__ __forceinline__ float dot(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ f3 cross(f3 a, f3 b) {
+    return mk(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+__device__ __forceinline__ float length(f3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ f3 normalize(f3 a) { float inv = 1.0f / sqrtf(dot(a, a)); return a * inv; }
+__device__ __forceinline__ float saturate(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+
+/* sincos: two-step Cody-Waite reduction by pi/2, Cephes single-precision polynomials */
+__device__ __forceinline__ void sincos_det(float x, float &s_out, float &c_out) {
+    const float TWO_OVER_PI = 0.6366197466850281f;
+    const float PIO2_HI = 1.5707963705062866f;
+    const float PIO2_LO = -4.371138828673793e-08f;
+    float kf = floorf(fmaf(x, TWO_OVER_PI, 0.5f));
+    int k = (int)kf;
+    float r = fmaf(-kf, PIO2_HI, x);
+    r = fmaf(-kf, PIO2_LO, r);
+    float r2 = r * r;
+    float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ps = fmaf(r2, ps, -1.6666654611e-1f);
+    float s = fmaf(r * r2, ps, r);
+    float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    pc = fmaf(r2, pc, 4.166664568298827e-2f);
+    float c = fmaf(r2 * r2, pc, fmaf(r2, -0.5f, 1.0f));
+    /* quadrant rotation without a switch: swap on odd k, negate by bit tests */
+    bool sw = k & 1;
+    float ss = sw ? c : s;
+    float cc = sw ? s : c;
+    s_out = (k & 2) ? -ss : ss;
+    c_out = ((k + 1) & 2) ? -cc : cc;
+}
+__device__ __forceinline__ float tan_det(float x) { float s, c; sincos_det(x, s, c); return s / c; }
+
+/* ---- Halton, RTrace/sampling.metal:97-122 ------------------------------------
+ * halton(i, d): f = 1; invB = 1.0f / b; while (i) { f *= invB; r += f * (i % b); i /= b; }
+ * The products f_k = f_{k-1} * invB are the same rounded sequence whatever i is,
+ * so they are compile-time constants here; the digits come out of divisions by a
+ * compile-time base (multiply-high + shift).  DIGITS covers i < 2^22 (B^DIGITS >=
+ * 2^22); larger i fall through to the generic loop, so the function is exact for
+ * every 32-bit index.  A zero digit adds f*0 = +0 and leaves r unchanged, which
+ * is why running all DIGITS steps equals the reference's early-exit loop.
+ */
+__host__ __device__ constexpr uint32_t rt_prime(int d) {
+    constexpr uint32_t P[24] = { 2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37,
+                                 41, 43, 47, 53, 59, 61, 67, 71, 73, 79, 83, 89 };
+    return P[d];
+}
+__host__ __device__ constexpr int rt_digits_for(uint32_t b, uint64_t limit) {
+    int k = 0; uint64_t p = 1;
+    while (p < limit) { p *= b; k++; }
+    return k;
+}
+__host__ __device__ constexpr float rt_halton_f(uint32_t b, int k) {   /* f after k+1 products */
+    float invB = 1.0f / (float)b;
+    float f = 1.0f;
+    for (int j = 0; j <= k; j++) f = f * invB;
+    return f;
+}
+
+template <int DIM>
+__device__ __forceinline__ float halton(uint32_t i) {
+    constexpr uint32_t B = rt_prime(DIM);
+    if (DIM == 0 && i < (1u << 24)) {
+        /* base 2: every partial sum is exact while i < 2^24 */
+        return (float)__brev(i) * 2.3283064365386963e-10f;
+    }
+    constexpr int DIGITS = rt_digits_for(B, 1ull << 22);
+    float r = 0.0f;
+#pragma unroll
+    for (int k = 0; k < DIGITS; k++) {
+        uint32_t q = i / B;
+        uint32_t dgt = i - q * B;
+        r = r + rt_halton_f(B, k) * (float)dgt;
+        i = q;
+    }
+    if (i > 0) {                                   /* never taken for i < 2^22 */
+        float invB = 1.0f / (float)B;
+        float f = rt_halton_f(B, DIGITS - 1);
+        while (i > 0) {
+            f = f * invB;
+            r = r + f * (float)(i % B);
+            i = i / B;
+        }
+    }
+    return r;
+}
+
+/* run-time dimension (self-test and mode B) */
+__device__ __noinline__ float halton_rt(uint32_t i, uint32_t d) {
+    const uint32_t P[24] = { 2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37,
+                             41, 43, 47, 53, 59, 61, 67, 71, 73, 79, 83, 89 };
+    uint32_t b = P[d];
+    float f = 1.0f, invB = 1.0f / (float)b, r = 0.0f;
+    while (i > 0) { f = f * invB; r = r + f * (float)(i % b); i = i / b; }
+    return r;
+}
+
+/* sampling.metal:68-75 */
+__device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+
+}  // namespace rt

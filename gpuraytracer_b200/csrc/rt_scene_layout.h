@@ -1,0 +1,88 @@
+/*
+ * rt_scene_layout.h -- layout of the PREPARED scene: what the prep kernel writes
+ * into HBM once per command and what every pathTrace block stages into shared
+ * memory (and, for the constant-bank variant, what is copied into c_isect).
+ * Shared by the kernels (pathtrace.cu) and the host shim (rtcuda.cpp).
+ *
+ * All sections are arrays of 32-bit words inside one flat buffer:
+ *
+ *   [0, RT_HDR_WORDS)               header: camera frame + counts   (floats / uints)
+ *   isect  : 12 words per triangle  v0.xyz e1.x | e1.yz e2.xy | e2.z 0 0 0
+ *            read with the SAME index by all lanes -> 3 broadcast 128-bit loads
+ *   shade  : RT_SHADE_ROWS rows of Tp words (structure of arrays, Tp = T rounded
+ *            up to 32): looked up with the per-lane primitive id after a hit,
+ *            so SoA keeps different ids on different banks
+ *   sphere : 4 words per sphere     center.xyz radius
+ *   sshade : RT_SSHADE_ROWS rows of Sp words
+ *   light  : 8 words per light      center.xyz 0 | color.xyz 0
+ */
+#ifndef RT_SCENE_LAYOUT_H
+#define RT_SCENE_LAYOUT_H
+
+#include <stdint.h>
+
+#define RT_HDR_WORDS     32
+/* header word indices */
+#define RT_HDR_CAM_O      0   /* 3: camera.position                                  */
+#define RT_HDR_CAM_U      3   /* 3: u = normalize(cross(up, w))                      */
+#define RT_HDR_CAM_V      6   /* 3: v = normalize(cross(w, u))                       */
+#define RT_HDR_CAM_W      9   /* 3: w = -normalize(direction)                        */
+#define RT_HDR_HALF_W    12   /* tan(fov/2)                                          */
+#define RT_HDR_HALF_H    13   /* halfWidth / float(res.x / res.y)                    */
+#define RT_HDR_RES_X     14   /* float(camera.resolution.x)                          */
+#define RT_HDR_RES_Y     15   /* float(camera.resolution.y)                          */
+#define RT_HDR_EXPOSURE  16   /* mode B: 1 / (1.2 * 2^ev100)                         */
+
+#define RT_ISECT_WORDS   12
+
+/* shade rows (per triangle) */
+#define RT_SH_NX          0   /* geometric normal, getTriangleNormal                 */
+#define RT_SH_RX          3   /* right   = normalize(cross(n, (0.0072,1,0.0034)))    */
+#define RT_SH_FX          6   /* forward = cross(right, n)                           */
+#define RT_SH_DR          9   /* diffuse.rgb                                         */
+#define RT_SH_ER         12   /* emissive.rgb                                        */
+#define RT_SH_FLAG       15   /* 1.0f when length(emissive) > 0                      */
+#define RT_SH_METAL      16   /* mode B */
+#define RT_SH_ROUGH      17   /* mode B */
+#define RT_SHADE_ROWS    18
+
+#define RT_SSH_DR         0
+#define RT_SSH_ER         3
+#define RT_SSH_FLAG       6
+#define RT_SSHADE_ROWS    7
+
+#define RT_LIGHT_WORDS    8
+
+#define RT_MAX_TRIANGLES 1024
+#define RT_MAX_SPHERES   1024
+#define RT_MAX_LIGHTS    16
+
+typedef struct RTSceneLayout {
+    uint32_t T, S, L;
+    uint32_t Tp, Sp;          /* padded to a multiple of 32                          */
+    uint32_t isect, shade, sphere, sshade, light;   /* section starts, in words      */
+    uint32_t words;           /* total size                                          */
+} RTSceneLayout;
+
+#if defined(__CUDACC__)
+#define RT_HD __host__ __device__ inline
+#else
+#define RT_HD static inline
+#endif
+
+RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
+    RTSceneLayout l;
+    l.T = T; l.S = S; l.L = L;
+    l.Tp = (T + 31u) & ~31u;
+    l.Sp = (S + 31u) & ~31u;
+    l.isect  = RT_HDR_WORDS;
+    l.shade  = l.isect + RT_ISECT_WORDS * l.Tp;
+    l.sphere = l.shade + RT_SHADE_ROWS * l.Tp;
+    l.sshade = l.sphere + 4u * l.Sp;
+    l.light  = l.sshade + RT_SSHADE_ROWS * l.Sp;
+    l.words  = l.light + RT_LIGHT_WORDS * L;
+    l.words  = (l.words + 3u) & ~3u;
+    return l;
+}
+
+#endif

@@ -1,0 +1,224 @@
+/*
+ * rt_detmath.h -- TEST INFRASTRUCTURE (oracle).  Not part of the product: only
+ * tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may build or call anything under oracle/.
+ *
+ * What this file is: the fp32 definition of everything the reference shaders
+ * get from OUTSIDE their own source, i.e. from the Metal standard library and
+ * from the Metal ray-tracing runtime, neither of which has source in
+ * /root/reference ("third-party arithmetic"):
+ *
+ *   dot / cross / length / normalize / saturate / sqrt     <metal_stdlib>
+ *   sincos / sin / cos / tan                               <metal_stdlib>
+ *   intersector<triangle_data>::intersect (closest / any)  <metal_raytracing>
+ *       call sites: RTrace/raytrace.metal:26-30,48-49,83-85
+ *                   Sources/gpuRaytracer/shaders.metal:459-483
+ *
+ * Metal's own versions are closed source and the reference builds with
+ * MTL_FAST_MATH=YES (RTrace.xcodeproj/project.pbxproj:198,256), so there is no
+ * bit-level ground truth to copy.  The rules fixed here are:
+ *
+ *   R1  all arithmetic is IEEE-754 binary32, round to nearest even, denormals
+ *       kept; `/` and sqrtf are correctly rounded.
+ *   R2  the LIBRARY functions below use fused multiply-add exactly where an
+ *       fmaf() is written, nowhere else.
+ *   R3  SHADER-level expressions (everything written in the .metal files) are
+ *       evaluated as C would evaluate them in float: one rounding per
+ *       operator, left to right, NO contraction.  That is what makes the
+ *       unmodified .metal source compiled by g++ (-ffp-contract=off
+ *       -fsingle-precision-constant, oracle/_ref) bit-identical to the C
+ *       restatement in rt_oracle.c and to the CUDA kernel.
+ *
+ * Build flags that these rules need: gcc -O2 -ffp-contract=off -fno-fast-math
+ * (-mfma only makes fmaf() an instruction instead of a libm call).
+ */
+#ifndef RT_DETMATH_H
+#define RT_DETMATH_H
+
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#ifdef __cplusplus
+#define RT_INLINE static inline
+#else
+#define RT_INLINE static inline
+#endif
+
+/* ---- <metal_stdlib> geometric functions ---------------------------------- */
+
+/* dot(a,b) = fma(az,bz, fma(ay,by, ax*bx)) */
+RT_INLINE float rt_dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return fmaf(az, bz, fmaf(ay, by, ax * bx));
+}
+
+/* cross(a,b): each component is  fma(p, q, -(r*s))  */
+RT_INLINE void rt_cross3(float ax, float ay, float az, float bx, float by, float bz,
+                         float *cx, float *cy, float *cz) {
+    *cx = fmaf(ay, bz, -(az * by));
+    *cy = fmaf(az, bx, -(ax * bz));
+    *cz = fmaf(ax, by, -(ay * bx));
+}
+
+/* length(v) = sqrt(dot(v,v)) */
+RT_INLINE float rt_length3(float x, float y, float z) {
+    return sqrtf(rt_dot3(x, y, z, x, y, z));
+}
+
+/* normalize(v) = v * (1 / sqrt(dot(v,v)))   (one sqrt, one division, three products) */
+RT_INLINE void rt_normalize3(float *x, float *y, float *z) {
+    float inv = 1.0f / sqrtf(rt_dot3(*x, *y, *z, *x, *y, *z));
+    *x = *x * inv; *y = *y * inv; *z = *z * inv;
+}
+
+/* saturate(x) = min(max(x,0),1); a NaN input gives 0 (fmaxf drops the NaN) */
+RT_INLINE float rt_saturate(float x) {
+    return fminf(fmaxf(x, 0.0f), 1.0f);
+}
+
+/* ---- <metal_stdlib> trigonometry ----------------------------------------- */
+/*
+ * sincos(x): Cody-Waite reduction by pi/2 in two steps, then the classic
+ * minimax polynomials on [-pi/4, pi/4] (single-precision Cephes coefficients).
+ * Accurate to about 1 ulp for |x| < 1e3, which covers phi = 2*pi*u, u in [0,1).
+ */
+#define RT_TWO_OVER_PI 0.6366197466850281f        /* (float)(2/pi), 0x3f22f983              */
+#define RT_PIO2_HI     1.5707963705062866f        /* (float)(pi/2), 0x3fc90fdb              */
+#define RT_PIO2_LO     (-4.371138828673793e-08f)  /* (float)(pi/2 - RT_PIO2_HI), 0xb33bbd2e */
+
+RT_INLINE void rt_sincosf(float x, float *s_out, float *c_out) {
+    float kf = floorf(fmaf(x, RT_TWO_OVER_PI, 0.5f));
+    int   k  = (int)kf;
+    float r  = fmaf(-kf, RT_PIO2_HI, x);
+    r        = fmaf(-kf, RT_PIO2_LO, r);
+    float r2 = r * r;
+    /* sin(r) = r + r*r2*(S1 + r2*(S2 + r2*S3)) */
+    float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ps       = fmaf(r2, ps, -1.6666654611e-1f);
+    float s  = fmaf(r * r2, ps, r);
+    /* cos(r) = 1 - r2/2 + r2*r2*(C1 + r2*(C2 + r2*C3)) */
+    float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    pc       = fmaf(r2, pc, 4.166664568298827e-2f);
+    float c  = fmaf(r2 * r2, pc, fmaf(r2, -0.5f, 1.0f));
+    switch (k & 3) {
+        case 0:  *s_out =  s; *c_out =  c; break;
+        case 1:  *s_out =  c; *c_out = -s; break;
+        case 2:  *s_out = -s; *c_out = -c; break;
+        default: *s_out = -c; *c_out =  s; break;
+    }
+}
+RT_INLINE float rt_sinf(float x) { float s, c; rt_sincosf(x, &s, &c); return s; }
+RT_INLINE float rt_cosf(float x) { float s, c; rt_sincosf(x, &s, &c); return c; }
+/* tan(x) = sin(x) / cos(x) */
+RT_INLINE float rt_tanf(float x) { float s, c; rt_sincosf(x, &s, &c); return s / c; }
+
+/* ---- <metal_raytracing> intersector ---------------------------------------
+ *
+ * Replacement for the hardware BVH query: a brute-force loop over the T
+ * triangles of the vertex buffer (stride 16 bytes, three vertices per
+ * triangle, primitive_id = triangle index; reference
+ * RTrace/computeShader.swift:47-66, RTrace/renderer.swift:51-57) with a
+ * division-free Moller-Trumbore test.  For triangle (v0,v1,v2), ray (o,d):
+ *
+ *     e1 = v1-v0   e2 = v2-v0
+ *     p  = cross(d, e2)        det = dot(e1, p)
+ *     tv = o - v0              U   = dot(tv, p)
+ *     q  = cross(tv, e1)       V   = dot(d, q)        N = dot(e2, q)
+ *     if det < 0 (sign bit set): U,V,N = -U,-V,-N ;   a = |det|
+ *
+ * (u,v,t) = (U,V,N)/a are never formed inside the loop.  The hit is accepted
+ * when
+ *     U >= 0  &&  V >= 0  &&  U+V <= a           inside, edges inclusive, no culling
+ *     N >= tmin*a                                  t >= tmin
+ *     N*bestD < bestN*a                            t <  best so far (strict)
+ * where (bestN,bestD) starts as (tmax,1), so the same comparison enforces
+ * t < tmax, and a tie between two triangles keeps the LOWER primitive id.
+ * det == 0 can never pass (it would need N >= 0 and N < 0).  The reported
+ * distance is the single division bestN/bestD after the loop.
+ *
+ * accept_any_intersection(true) (shadow rays, raytrace.metal:83) answers only
+ * hit / no hit; it is the same test and may stop at the first accepted
+ * triangle.  Sphere primitives (config 4, an extension the live reference
+ * kernels do not have; arithmetic after shaders_old.metal:108-136) are tested
+ * after the triangles and carry primitive ids T..T+S-1; see rt_sphere_test.
+ */
+typedef struct {
+    int      hit;           /* 0 = intersection_type::none */
+    float    distance;
+    uint32_t primitive_id;
+} rt_hit;
+
+/* One triangle test in the scaled form above.  Returns 1 and updates
+ * (bestN,bestD) when the triangle is the new closest hit. */
+RT_INLINE int rt_triangle_test(const float *v0, const float *v1, const float *v2,
+                               const float o[3], const float d[3], float tmin,
+                               float *bestN, float *bestD) {
+    float e1x = v1[0] - v0[0], e1y = v1[1] - v0[1], e1z = v1[2] - v0[2];
+    float e2x = v2[0] - v0[0], e2y = v2[1] - v0[1], e2z = v2[2] - v0[2];
+    float px, py, pz, qx, qy, qz;
+    rt_cross3(d[0], d[1], d[2], e2x, e2y, e2z, &px, &py, &pz);
+    float det = rt_dot3(e1x, e1y, e1z, px, py, pz);
+    float tx = o[0] - v0[0], ty = o[1] - v0[1], tz = o[2] - v0[2];
+    float U = rt_dot3(tx, ty, tz, px, py, pz);
+    rt_cross3(tx, ty, tz, e1x, e1y, e1z, &qx, &qy, &qz);
+    float V = rt_dot3(d[0], d[1], d[2], qx, qy, qz);
+    float N = rt_dot3(e2x, e2y, e2z, qx, qy, qz);
+    if (signbit(det)) { U = -U; V = -V; N = -N; }
+    float a = fabsf(det);
+    if (U >= 0.0f && V >= 0.0f && U + V <= a && N >= tmin * a && N * *bestD < *bestN * a) {
+        *bestN = N; *bestD = a;
+        return 1;
+    }
+    return 0;
+}
+
+/* Sphere test, same rational bookkeeping.  With m = o - c, A = dot(d,d),
+ * B = dot(m,d), C = dot(m,m) - r*r the roots are t = (-B -+ sqrt(B*B - A*C))/A.
+ * The nearer root is tried first, then the farther one (so a ray that starts
+ * inside a sphere hits its far wall; shaders_old.metal:121-122 picks
+ * min(t1,t2) whenever either is positive, which is wrong from inside). */
+RT_INLINE int rt_sphere_test(const float c[3], float radius,
+                             const float o[3], const float d[3], float tmin,
+                             float *bestN, float *bestD) {
+    float mx = o[0] - c[0], my = o[1] - c[1], mz = o[2] - c[2];
+    float A = rt_dot3(d[0], d[1], d[2], d[0], d[1], d[2]);
+    float B = rt_dot3(mx, my, mz, d[0], d[1], d[2]);
+    float C = fmaf(-radius, radius, rt_dot3(mx, my, mz, mx, my, mz));
+    float disc = fmaf(B, B, -(A * C));
+    if (!(disc >= 0.0f)) return 0;
+    float sq = sqrtf(disc);
+    float N0 = -B - sq, N1 = -B + sq;   /* scaled by A > 0 */
+    if (N0 >= tmin * A && N0 * *bestD < *bestN * A) { *bestN = N0; *bestD = A; return 1; }
+    if (N1 >= tmin * A && N1 * *bestD < *bestN * A) { *bestN = N1; *bestD = A; return 1; }
+    return 0;
+}
+
+/* vertices: 3*T entries of 4 floats (simd_float3, 16-byte stride);
+ * spheres: S entries of 20 floats (SphereGPU, 80 bytes: center@0, radius@64). */
+RT_INLINE rt_hit rt_intersect(const float *vertices, uint32_t numTriangles,
+                              const float *spheres, uint32_t numSpheres,
+                              const float o[3], const float d[3],
+                              float tmin, float tmax, int acceptAny) {
+    rt_hit h; h.hit = 0; h.distance = 0.0f; h.primitive_id = 0;
+    float bestN = tmax, bestD = 1.0f;
+    for (uint32_t i = 0; i < numTriangles; i++) {
+        const float *v = vertices + (size_t)i * 12;
+        if (rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &bestN, &bestD)) {
+            h.hit = 1; h.primitive_id = i;
+            if (acceptAny) break;
+        }
+    }
+    if (!(acceptAny && h.hit)) {
+        for (uint32_t j = 0; j < numSpheres; j++) {
+            const float *s = spheres + (size_t)j * 20;
+            if (rt_sphere_test(s, s[16], o, d, tmin, &bestN, &bestD)) {
+                h.hit = 1; h.primitive_id = numTriangles + j;
+                if (acceptAny) break;
+            }
+        }
+    }
+    if (h.hit) h.distance = bestN / bestD;
+    return h;
+}
+
+#endif /* RT_DETMATH_H */

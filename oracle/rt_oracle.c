@@ -1,0 +1,356 @@
+/*
+ * rt_oracle.c -- TEST INFRASTRUCTURE.  CPU restatement of the reference kernel
+ * `pathTrace` (mode A), one pixel at a time, OpenMP over rows.
+ *
+ * Follows, statement by statement:
+ *     RTrace/raytrace.metal:22-109        kernel body
+ *     RTrace/sampling.metal:16-26         getTriangleNormal
+ *     RTrace/sampling.metal:39-49         sampleCosineWeightedHemisphere
+ *     RTrace/sampling.metal:51-66         alignHemisphereWithNormal
+ *     RTrace/sampling.metal:68-75         hash
+ *     RTrace/sampling.metal:97-122        primes[], halton
+ *     RTrace/sampling.metal:125-157       generateCameraRay
+ *     RTrace/sampling.metal:198-236       sampleAreaLight
+ *     RTrace/image.swift:40-65            tone map (resolve)
+ * Arithmetic rules: rt_detmath.h (R1-R3).  Shader-level expressions below are
+ * written operator by operator in the order MSL parses them; do not "simplify".
+ * Must be compiled with -ffp-contract=off and without -ffast-math.
+ *
+ * Extensions that the reference kernel does not have, all inert at the
+ * reference's settings: row tiles (row0/rows), spp / firstSample / bounces as
+ * parameters, progressive accumulation, sphere primitives and more than one
+ * light (config 4; see DESIGN.md "oracle-defined extensions").
+ */
+#include "rt_oracle.h"
+#include "rt_detmath.h"
+
+#include <stdlib.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#if defined(__FAST_MATH__)
+#error "the oracle must not be built with -ffast-math"
+#endif
+
+typedef struct { float x, y, z; } f3;
+
+static inline f3 f3_make(float x, float y, float z) { f3 r = { x, y, z }; return r; }
+static inline f3 f3_ld(const simd_float3 *p) { return f3_make(p->x, p->y, p->z); }
+static inline f3 f3_add(f3 a, f3 b) { return f3_make(a.x + b.x, a.y + b.y, a.z + b.z); }
+static inline f3 f3_sub(f3 a, f3 b) { return f3_make(a.x - b.x, a.y - b.y, a.z - b.z); }
+static inline f3 f3_mul(f3 a, f3 b) { return f3_make(a.x * b.x, a.y * b.y, a.z * b.z); }
+static inline f3 f3_scale(f3 a, float s) { return f3_make(a.x * s, a.y * s, a.z * s); }
+static inline f3 f3_neg(f3 a) { return f3_make(-a.x, -a.y, -a.z); }
+static inline float f3_dot(f3 a, f3 b) { return rt_dot3(a.x, a.y, a.z, b.x, b.y, b.z); }
+static inline f3 f3_cross(f3 a, f3 b) { f3 r; rt_cross3(a.x, a.y, a.z, b.x, b.y, b.z, &r.x, &r.y, &r.z); return r; }
+static inline f3 f3_normalize(f3 a) { rt_normalize3(&a.x, &a.y, &a.z); return a; }
+static inline float f3_length(f3 a) { return rt_length3(a.x, a.y, a.z); }
+
+/* sampling.metal:68-75 */
+uint32_t rt_oracle_hash(uint32_t x) {
+    x ^= x >> 16;
+    x *= 0x7feb352dU;
+    x ^= x >> 15;
+    x *= 0x846ca68bU;
+    x ^= x >> 16;
+    return x;
+}
+
+/* sampling.metal:97-104 */
+static const uint32_t rt_primes[24] = {
+    2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37,
+    41, 43, 47, 53, 59, 61, 67, 71, 73, 79, 83, 89
+};
+
+/* sampling.metal:107-122 */
+float rt_oracle_halton(uint32_t i, uint32_t d) {
+    uint32_t b = rt_primes[d];
+    float f = 1.0f;
+    float invB = 1.0f / (float)b;
+    float r = 0.0f;
+    while (i > 0) {
+        f = f * invB;
+        r = r + f * (float)(i % b);
+        i = i / b;
+    }
+    return r;
+}
+
+/* sampling.metal:16-26 */
+static inline f3 triangle_normal(const simd_float3 *vertices, uint32_t primitiveId) {
+    f3 v0 = f3_ld(&vertices[primitiveId * 3 + 0]);
+    f3 v1 = f3_ld(&vertices[primitiveId * 3 + 1]);
+    f3 v2 = f3_ld(&vertices[primitiveId * 3 + 2]);
+    f3 edge1 = f3_sub(v1, v0);
+    f3 edge2 = f3_sub(v2, v0);
+    return f3_normalize(f3_cross(edge1, edge2));
+}
+
+/* sampling.metal:39-49 */
+static inline f3 sample_cosine_hemisphere(float ux, float uy) {
+    float phi = (2.0f * 3.14159265358979323846264338327950288f) * ux;
+    float sin_phi, cos_phi;
+    rt_sincosf(phi, &sin_phi, &cos_phi);
+    float cos_theta = sqrtf(uy);
+    float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+    return f3_make(sin_theta * cos_phi, cos_theta, sin_theta * sin_phi);
+}
+
+/* sampling.metal:51-66 */
+static inline f3 align_hemisphere(f3 sample, f3 normal) {
+    f3 up = normal;
+    f3 right = f3_normalize(f3_cross(normal, f3_make(0.0072f, 1.0f, 0.0034f)));
+    f3 forward = f3_cross(right, up);
+    return f3_add(f3_add(f3_scale(right, sample.x), f3_scale(up, sample.y)), f3_scale(forward, sample.z));
+}
+
+/* sampling.metal:125-157.  Note the INTEGER division in aspectRatio (:132). */
+static inline void camera_ray(const CameraGPU *camera, uint32_t ix, uint32_t iy, float jx, float jy,
+                              f3 *origin, f3 *direction) {
+    int x = (int)ix;
+    int y = (int)iy;
+    float aspectRatio = (float)(camera->resolution.x / camera->resolution.y);
+    float halfWidth = rt_tanf(camera->horizontalFov / 2.0f);
+    float halfHeight = halfWidth / aspectRatio;
+
+    f3 w = f3_neg(f3_normalize(f3_ld(&camera->direction)));
+    f3 u = f3_normalize(f3_cross(f3_ld(&camera->up), w));
+    f3 v = f3_normalize(f3_cross(w, u));
+
+    float s = (((float)x + jx) / (float)camera->resolution.x) * 2.0f - 1.0f;
+    float t = -((((float)y + jy) / (float)camera->resolution.y) * 2.0f - 1.0f);
+
+    f3 dir = f3_normalize(f3_sub(f3_add(f3_scale(u, s * halfWidth), f3_scale(v, t * halfHeight)), w));
+    *origin = f3_ld(&camera->position);
+    *direction = dir;
+}
+
+/* sampling.metal:198-236.  The 0.5 x 0.5 extent and the -y normal are the
+ * reference's own literals (:207-209); light.width / light.depth are ignored. */
+static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float uy, f3 position,
+                                   f3 *lightDirection, float *lightDistance) {
+    ux = ux * 2.0f - 1.0f;
+    uy = uy * 2.0f - 1.0f;
+
+    f3 normal = f3_make(0.0f, -1.0f, 0.0f);
+    f3 right = f3_make(0.25f, 0.0f, 0.0f);
+    f3 up = f3_make(0.0f, 0.0f, 0.25f);
+    f3 samplePosition = f3_add(f3_add(f3_ld(&light->center), f3_scale(right, ux)), f3_scale(up, uy));
+
+    f3 ld = f3_sub(samplePosition, position);
+    float dist = f3_length(ld);
+    float inverseLightDistance = 1.0f / fmaxf(dist, 1e-3f);
+    ld = f3_scale(ld, inverseLightDistance);
+
+    f3 lightColor = f3_make(light->color.x, light->color.y, light->color.z);
+    lightColor = f3_scale(lightColor, inverseLightDistance * inverseLightDistance);
+    lightColor = f3_scale(lightColor, rt_saturate(f3_dot(f3_neg(ld), normal)));
+
+    *lightDirection = ld;
+    *lightDistance = dist;
+    return lightColor;
+}
+
+typedef struct {
+    const CameraGPU *camera;
+    const MaterialGPU *materials;
+    const SquareLightGPU *lights;
+    const simd_float3 *vertices;
+    const SphereGPU *spheres;
+    uint32_t T, S, L;
+    int bounces;
+} scene_view;
+
+static inline rt_hit scene_intersect(const scene_view *sc, f3 o, f3 d, float tmin, float tmax, int any) {
+    float oo[3] = { o.x, o.y, o.z }, dd[3] = { d.x, d.y, d.z };
+    return rt_intersect((const float *)sc->vertices, sc->T, (const float *)sc->spheres, sc->S,
+                        oo, dd, tmin, tmax, any);
+}
+
+/* One camera sample: raytrace.metal:37-102.  Returns accumulatedColor. */
+static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint32_t offset, uint32_t n,
+                            uint64_t *cnt) {
+    float uvx = rt_oracle_halton(offset + n, 0);
+    float uvy = rt_oracle_halton(offset + n, 1);
+
+    f3 ro, rd;
+    camera_ray(&sc->camera[0], ix, iy, uvx, uvy, &ro, &rd);
+    const float rmin = 0.001f, rmax = 1000.0f;     /* sampling.metal:154-155; kept across bounces */
+
+    f3 accumulatedColor = f3_make(0.0f, 0.0f, 0.0f);
+    f3 color = f3_make(1.0f, 1.0f, 1.0f);
+
+    for (int bounce = 0; bounce < sc->bounces; bounce++) {
+        cnt[RT_CNT_CLOSEST_RAYS]++;
+        rt_hit hit = scene_intersect(sc, ro, rd, rmin, rmax, 0);
+        if (!hit.hit) break;
+
+        /* materials[primitive_id]; sphere primitives (extension) carry their own */
+        const MaterialGPU *m = hit.primitive_id < sc->T ? &sc->materials[hit.primitive_id]
+                                                        : &sc->spheres[hit.primitive_id - sc->T].material;
+        if (f3_length(f3_ld(&m->emissive)) > 0.0f) {
+            accumulatedColor = f3_ld(&m->emissive);      /* assignment, raytrace.metal:59 */
+            break;
+        }
+        cnt[RT_CNT_SHADED_BOUNCES]++;
+
+        f3 normal;
+        if (hit.primitive_id < sc->T) {
+            normal = triangle_normal(sc->vertices, hit.primitive_id);
+        } else {  /* extension: outward sphere normal at the un-offset hit point */
+            f3 hp = f3_add(ro, f3_scale(rd, hit.distance));
+            normal = f3_normalize(f3_sub(hp, f3_ld(&sc->spheres[hit.primitive_id - sc->T].center)));
+        }
+        f3 P = f3_add(f3_add(ro, f3_scale(rd, hit.distance)), f3_scale(normal, 1e-3f));
+
+        float wx = rt_oracle_halton(offset + n, 2 + bounce * 5 + 0);
+        float wy = rt_oracle_halton(offset + n, 2 + bounce * 5 + 1);
+        color = f3_mul(color, f3_make(m->diffuse.x, m->diffuse.y, m->diffuse.z));
+
+        /* reference: lights[0] only (raytrace.metal:22); extension: every light,
+         * same w, one shadow ray each, summed in index order */
+        for (uint32_t l = 0; l < sc->L; l++) {
+            f3 ldir; float ldist;
+            f3 lightColor = sample_area_light(&sc->lights[l], wx, wy, P, &ldir, &ldist);
+            lightColor = f3_scale(lightColor, rt_saturate(f3_dot(normal, ldir)));
+            /* default-constructed ray: min_distance = 0 (raytrace.metal:79-82) */
+            cnt[RT_CNT_SHADOW_RAYS]++;
+            rt_hit sh = scene_intersect(sc, P, ldir, 0.0f, ldist - 1e-3f, 1);
+            if (!sh.hit) accumulatedColor = f3_add(accumulatedColor, f3_mul(lightColor, color));
+        }
+
+        float ux = rt_oracle_halton(offset + n, 2 + bounce * 5 + 2);
+        float uy = rt_oracle_halton(offset + n, 2 + bounce * 5 + 3);
+        f3 sd = sample_cosine_hemisphere(ux, uy);
+        sd = align_hemisphere(sd, normal);
+        ro = P;
+        rd = sd;
+    }
+    cnt[RT_CNT_PATHS]++;
+    return accumulatedColor;
+}
+
+static int check_params(const RTLaunchParams *p) {
+    if (!p) return RT_ERR_INVALID_ARGUMENT;
+    if (p->width <= 0 || p->height <= 0 || p->row0 < 0 || p->rows < 0 || p->row0 + p->rows > p->height)
+        return RT_ERR_INVALID_ARGUMENT;
+    return RT_OK;
+}
+
+int rt_oracle_pathtrace(const CameraGPU *cameras, const MaterialGPU *materials,
+                        const SquareLightGPU *lights, const simd_float3 *vertices,
+                        const SphereGPU *spheres, const uint32_t *offsets,
+                        float *out, const RTLaunchParams *p,
+                        uint64_t counters[RT_CNT_COUNT], int nthreads) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (!cameras || !materials || !lights || !vertices || !offsets || !out) return RT_ERR_INVALID_ARGUMENT;
+    if (p->spp == 0 || p->numLights == 0) return RT_ERR_INVALID_ARGUMENT;
+    if (p->bounces < 1 || p->bounces > 4) return RT_ERR_UNSUPPORTED;   /* primes[2+5b+3] must exist */
+    if (p->numSpheres && !spheres) return RT_ERR_INVALID_ARGUMENT;
+
+    scene_view sc = { cameras, materials, lights, vertices, spheres,
+                      p->numTriangles, p->numSpheres, p->numLights, p->bounces };
+    uint64_t total[RT_CNT_COUNT] = { 0 };
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+    nthreads = 1;
+#endif
+    const int W = p->width;
+
+#pragma omp parallel num_threads(nthreads)
+    {
+        uint64_t cnt[RT_CNT_COUNT] = { 0 };
+#pragma omp for schedule(dynamic, 1)
+        for (int ly = 0; ly < p->rows; ly++) {
+            const uint32_t iy = (uint32_t)(p->row0 + ly);
+            for (int x = 0; x < W; x++) {
+                const size_t px = (size_t)ly * W + x;
+                const uint32_t offset = offsets[px];          /* raytrace.metal:37 */
+                float *o = out + px * 4;
+                f3 luminance = p->accumulate ? f3_make(o[0], o[1], o[2]) : f3_make(0.0f, 0.0f, 0.0f);
+                for (uint32_t k = 0; k < p->spp; k++) {
+                    uint32_t n = p->firstSample + k;
+                    f3 a = trace_path(&sc, (uint32_t)x, iy, offset, n, cnt);
+                    luminance = f3_add(luminance, a);          /* raytrace.metal:103 */
+                }
+                if (p->accumulate) {
+                    o[0] = luminance.x; o[1] = luminance.y; o[2] = luminance.z;
+                    o[3] = (float)(p->firstSample + p->spp);
+                } else {
+                    float samples = (float)p->spp;             /* raytrace.metal:106 */
+                    o[0] = luminance.x / samples; o[1] = luminance.y / samples; o[2] = luminance.z / samples;
+                    o[3] = 1.0f;                               /* raytrace.metal:109 */
+                }
+            }
+        }
+#pragma omp critical
+        for (int c = 0; c < RT_CNT_COUNT; c++) total[c] += cnt[c];
+    }
+    if (counters) for (int c = 0; c < RT_CNT_COUNT; c++) counters[c] = total[c];
+    return RT_OK;
+}
+
+/* ---- exported pieces for known-answer tests --------------------------------- */
+void rt_oracle_camera_ray(const CameraGPU *cam, uint32_t x, uint32_t y, float jx, float jy,
+                          float origin[3], float dir[3]) {
+    f3 o, d;
+    camera_ray(cam, x, y, jx, jy, &o, &d);
+    origin[0] = o.x; origin[1] = o.y; origin[2] = o.z;
+    dir[0] = d.x; dir[1] = d.y; dir[2] = d.z;
+}
+
+void rt_oracle_sample_area_light(const SquareLightGPU *light, float ux, float uy, const float pos[3],
+                                 float color[3], float ldir[3], float *ldist) {
+    f3 d; float dist;
+    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist);
+    color[0] = c.x; color[1] = c.y; color[2] = c.z;
+    ldir[0] = d.x; ldir[1] = d.y; ldir[2] = d.z;
+    *ldist = dist;
+}
+
+void rt_oracle_cosine_hemisphere(float ux, float uy, const float normal[3], float out[3]) {
+    f3 s = sample_cosine_hemisphere(ux, uy);
+    s = align_hemisphere(s, f3_make(normal[0], normal[1], normal[2]));
+    out[0] = s.x; out[1] = s.y; out[2] = s.z;
+}
+
+void rt_oracle_sincos(float x, float *s, float *c) { rt_sincosf(x, s, c); }
+
+int rt_oracle_intersect(const simd_float3 *vertices, uint32_t numTriangles,
+                        const SphereGPU *spheres, uint32_t numSpheres,
+                        const float o[3], const float d[3], float tmin, float tmax,
+                        int acceptAny, float *distance, uint32_t *primitive_id) {
+    rt_hit h = rt_intersect((const float *)vertices, numTriangles, (const float *)spheres, numSpheres,
+                            o, d, tmin, tmax, acceptAny);
+    if (distance) *distance = h.distance;
+    if (primitive_id) *primitive_id = h.primitive_id;
+    return h.hit;
+}
+
+/* RTrace/image.swift:40-65.  pow() is the one place the host image writer uses
+ * libm; the GPU resolve kernel is checked against this with +-1 LSB. */
+void rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels) {
+    const float exposure = 2.0f, gamma = 2.2f;
+    for (uint64_t i = 0; i < npixels; i++) {
+        for (int c = 0; c < 3; c++) {
+            float value = rgba[i * 4 + c];
+            value *= exposure;
+            value = value / (value + 1.0f);
+            value = powf(value, 1.0f / gamma);
+            value = fmaxf(0.0f, fminf(1.0f, value));
+            out[i * 4 + c] = (uint8_t)(value * 255.0f);
+        }
+        out[i * 4 + 3] = 255;
+    }
+}
+
+int rt_oracle_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}

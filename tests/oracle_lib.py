@@ -1,0 +1,77 @@
+"""ctypes access to oracle/liboracle.so -- the CHECKER.  Only tests/, smoke() and
+bench.py's cpu_baseline / --impl reference legs import this module."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
+if not os.path.exists(_PATH):
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+lib = C.CDLL(_PATH)
+
+
+class RTLaunchParams(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("row0", C.c_int32), ("rows", C.c_int32),
+                ("spp", C.c_uint32), ("firstSample", C.c_uint32), ("bounces", C.c_int32),
+                ("accumulate", C.c_int32), ("numTriangles", C.c_uint32), ("numSpheres", C.c_uint32),
+                ("numLights", C.c_uint32), ("cameraRays", C.c_uint32), ("misSamples", C.c_uint32),
+                ("variant", C.c_uint32), ("reserved", C.c_uint32 * 2)]
+
+
+lib.rt_oracle_halton.restype = C.c_float
+lib.rt_oracle_halton.argtypes = [C.c_uint32, C.c_uint32]
+lib.rt_oracle_hash.restype = C.c_uint32
+lib.rt_oracle_hash.argtypes = [C.c_uint32]
+lib.rt_oracle_max_threads.restype = C.c_int
+
+
+def vp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def cornell(width, height, light_size=1.0):
+    cam = np.zeros(64, np.uint8); mats = np.zeros(36 * 48, np.uint8)
+    light = np.zeros(64, np.uint8); verts = np.zeros(108 * 16, np.uint8)
+    lib.rt_fixture_cornell(width, height, C.c_float(light_size), vp(cam), vp(mats), vp(light), vp(verts))
+    return dict(camera=cam, materials=mats, lights=light, vertices=verts, spheres=None, T=36, S=0, L=1)
+
+
+def spheres(width, height, seed=12345, n=256):
+    cam = np.zeros(64, np.uint8); mats = np.zeros(18 * 48, np.uint8)
+    lights = np.zeros(4 * 64, np.uint8); verts = np.zeros(54 * 16, np.uint8); sph = np.zeros(n * 80, np.uint8)
+    lib.rt_fixture_spheres(width, height, C.c_uint32(seed), C.c_uint32(n), vp(cam), vp(mats), vp(lights), vp(verts), vp(sph))
+    return dict(camera=cam, materials=mats, lights=lights, vertices=verts, spheres=sph, T=18, S=n, L=4)
+
+
+def offsets(width, row0, rows, seed=1):
+    off = np.zeros(width * rows, np.uint32)
+    lib.rt_fixture_offsets(vp(off), width, row0, rows, C.c_uint32(seed))
+    return off
+
+
+def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, bounces=3, accumulate=False,
+              out=None, off=None, seed=1, nthreads=0):
+    """Returns (image float32 [rows,width,4], counters uint64[8])."""
+    rows = height - row0 if rows is None else rows
+    if off is None:
+        off = offsets(width, row0, rows, seed)
+    if out is None:
+        out = np.zeros((rows, width, 4), np.float32)
+    cnt = np.zeros(8, np.uint64)
+    p = RTLaunchParams(width, height, row0, rows, spp, first_sample, bounces, int(accumulate),
+                       scene["T"], scene["S"], scene["L"], 6, 300, 0)
+    rc = lib.rt_oracle_pathtrace(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
+                                 vp(scene["vertices"]), vp(scene["spheres"]), vp(off), vp(out), C.byref(p),
+                                 vp(cnt), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_pathtrace returned {rc}")
+    return out, cnt
+
+
+def flops(cnt, T, S):
+    """F = 45*T*(Rc+Rs) + 18*S*(Rc+Rs) + 200*B + 60*P."""
+    P, Rc, Rs, B = (int(cnt[i]) for i in range(4))
+    return 45 * T * (Rc + Rs) + 18 * S * (Rc + Rs) + 200 * B + 60 * P
