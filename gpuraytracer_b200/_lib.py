@@ -25,6 +25,7 @@ INDEX_CAMERA, INDEX_MATERIALS, INDEX_LIGHTS, INDEX_VERTICES, INDEX_PIXELS = 0, 1
 INDEX_ACCEL, INDEX_DEBUG, INDEX_SPHERES, INDEX_OUTPUT, INDEX_OFFSETS = 5, 6, 7, 16, 17
 FORMAT_RGBA32_FLOAT, FORMAT_R32_UINT = 1, 2
 VARIANT_DEFAULT, VARIANT_SMEM, VARIANT_CONST = 0, 1, 2
+VARIANT_COUNT_RAYS = 0x100
 
 
 class RTLaunchParams(C.Structure):
@@ -32,7 +33,7 @@ class RTLaunchParams(C.Structure):
                 ("spp", C.c_uint32), ("firstSample", C.c_uint32), ("bounces", C.c_int32),
                 ("accumulate", C.c_int32), ("numTriangles", C.c_uint32), ("numSpheres", C.c_uint32),
                 ("numLights", C.c_uint32), ("cameraRays", C.c_uint32), ("misSamples", C.c_uint32),
-                ("variant", C.c_uint32), ("reserved", C.c_uint32 * 2)]
+                ("variant", C.c_uint32), ("tileRows", C.c_uint32), ("tileStride", C.c_uint32)]
 
 
 class RTDeviceInfo(C.Structure):

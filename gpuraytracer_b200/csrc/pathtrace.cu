@@ -257,11 +257,6 @@ __device__ __forceinline__ f3 sample_cosine_hemisphere(float ux, float uy) {
 #define RT_BLOCK_H 8
 #define RT_BLOCK_THREADS 128
 
-template <bool CONST_BANK, int MAXB>
-__device__ __forceinline__ f3 trace_path(const SceneRef<CONST_BANK> &sc, const float *__restrict__ sm,
-                                         const RTSceneLayout &lay, int bounces, uint32_t numLights,
-                                         uint32_t px, uint32_t py, uint32_t i);
-
 template <int B>
 struct HaltonDims {
     __device__ static __forceinline__ void light(uint32_t i, float &a, float &b) { a = halton<2 + 5 * B>(i); b = halton<3 + 5 * B>(i); }
@@ -269,11 +264,14 @@ struct HaltonDims {
 };
 
 /* one bounce of raytrace.metal:47-101; returns false when the path ends */
-template <bool CONST_BANK, int B>
+struct Counters { uint32_t closest, shadow, shaded; };
+
+template <bool CONST_BANK, int B, bool COUNT>
 __device__ __forceinline__ bool bounce_step(const SceneRef<CONST_BANK> &sc, const float *__restrict__ sm,
                                             const RTSceneLayout &lay, uint32_t numLights, uint32_t i,
-                                            f3 &ro, f3 &rd, f3 &color, f3 &acc) {
+                                            f3 &ro, f3 &rd, f3 &color, f3 &acc, Counters &cnt) {
     float dist; uint32_t id;
+    if (COUNT) cnt.closest++;
     if (!closest_hit<CONST_BANK>(sc, ro, rd, 0.001f, 1000.0f, dist, id)) return false;     /* :51-53 */
 
     f3 normal, right, fwd, diffuse;
@@ -302,6 +300,7 @@ __device__ __forceinline__ bool bounce_step(const SceneRef<CONST_BANK> &sc, cons
         diffuse = mk(sh[(RT_SSH_DR + 0) * lay.Sp], sh[(RT_SSH_DR + 1) * lay.Sp], sh[(RT_SSH_DR + 2) * lay.Sp]);
     }
     f3 P = (ro + rd * dist) + normal * 1e-3f;                                               /* :67 */
+    if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
 
     float wx, wy;
     HaltonDims<B>::light(i, wx, wy);                                                        /* :72-73 */
@@ -324,10 +323,11 @@ __device__ __forceinline__ bool bounce_step(const SceneRef<CONST_BANK> &sc, cons
     return true;
 }
 
-template <bool CONST_BANK>
+template <bool CONST_BANK, bool COUNT>
 __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                float4 *__restrict__ out, const RTLaunchParams p,
-                                               const RTSceneLayout lay, float *sm) {
+                                               const RTSceneLayout lay, float *sm,
+                                               unsigned long long *__restrict__ counters) {
     /* stage the prepared scene HBM -> shared memory (coalesced 128-bit copies) */
     {
         const float4 *src = (const float4 *)scene;
@@ -342,7 +342,9 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
     const uint32_t x = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4 + (lane >> 3);
     if (x >= (uint32_t)p.width || ly >= (uint32_t)p.rows) return;
-    const uint32_t y = (uint32_t)p.row0 + ly;
+    /* contiguous rows, or interleaved row tiles (multi-GPU load balance) */
+    const uint32_t y = p.tileRows ? (uint32_t)p.row0 + (ly / p.tileRows) * p.tileStride + (ly % p.tileRows)
+                                  : (uint32_t)p.row0 + ly;
     const size_t pix = (size_t)ly * (uint32_t)p.width + x;
 
     SceneRef<CONST_BANK> sc;
@@ -359,6 +361,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
     const float fx = (float)(int)x, fy = (float)(int)y;
 
     const uint32_t offset = offsets[pix];                               /* raytrace.metal:37, hoisted */
+    Counters cnt = { 0u, 0u, 0u };
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (p.accumulate) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 
@@ -375,10 +378,10 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
         f3 color = mk(1.0f, 1.0f, 1.0f);
         const int nb = p.bounces;
         do {
-            if (!bounce_step<CONST_BANK, 0>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 2) break;
-            if (!bounce_step<CONST_BANK, 1>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 3) break;
-            if (!bounce_step<CONST_BANK, 2>(sc, sm, lay, p.numLights, i, ro, rd, color, acc) || nb < 4) break;
-            bounce_step<CONST_BANK, 3>(sc, sm, lay, p.numLights, i, ro, rd, color, acc);
+            if (!bounce_step<CONST_BANK, 0, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 2) break;
+            if (!bounce_step<CONST_BANK, 1, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 3) break;
+            if (!bounce_step<CONST_BANK, 2, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 4) break;
+            bounce_step<CONST_BANK, 3, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt);
         } while (0);
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
@@ -391,21 +394,25 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
         o = make_float4(lum.x / samples, lum.y / samples, lum.z / samples, 1.0f);
     }
     out[pix] = o;
+    if (COUNT) {   /* exact work counters for the FLOP accounting; per-thread totals fit 32 bits */
+        atomicAdd(&counters[0], (unsigned long long)p.spp);
+        atomicAdd(&counters[1], (unsigned long long)cnt.closest);
+        atomicAdd(&counters[2], (unsigned long long)cnt.shadow);
+        atomicAdd(&counters[3], (unsigned long long)cnt.shaded);
+    }
 }
 
-extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
-pathTrace_smem(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
-               const RTLaunchParams p, const RTSceneLayout lay) {
-    extern __shared__ __align__(16) float sm[];
-    pathtrace_body<false>(scene, offsets, out, p, lay, sm);
-}
-
-extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
-pathTrace_const(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
-                const RTLaunchParams p, const RTSceneLayout lay) {
-    extern __shared__ __align__(16) float sm[];
-    pathtrace_body<true>(scene, offsets, out, p, lay, sm);
-}
+#define RT_PATHTRACE_ENTRY(name, CONST_BANK, COUNT)                                                              \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)                                            \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        pathtrace_body<CONST_BANK, COUNT>(scene, offsets, out, p, lay, sm, counters);                            \
+    }
+RT_PATHTRACE_ENTRY(pathTrace_smem, false, false)
+RT_PATHTRACE_ENTRY(pathTrace_const, true, false)
+RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true)
+RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true)
 
 /* ----------------------------------------------------------------- resolve ---- */
 /* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.

@@ -49,6 +49,7 @@ class Renderer:
                                                 C.byref(accel)), "rtAccelerationStructureCreate")
         self.accel = accel
         self.last_command = None
+        self.debug_buffer = None
 
     def params(self, **over):
         p = default_params(self.width, self.height, row0=self.row0, rows=self.rows,
@@ -70,7 +71,14 @@ class Renderer:
             cmd.set_buffer(self.spheres_buffer, 0, L.INDEX_SPHERES)
         cmd.set_buffer(self.render_buffer, 0, L.INDEX_OUTPUT)          # setTexture(renderTexture, 0)
         cmd.set_buffer(self.random_buffer, 0, L.INDEX_OFFSETS)         # setTexture(randomTexture, 1)
-        cmd.set_params(self.params(**over))
+        params = self.params(**over)
+        if params.variant & L.VARIANT_COUNT_RAYS:
+            # the reference binds a debug buffer at index 6 and never writes it (renderer.swift:128);
+            # the counting variant uses it for the exact ray counters
+            if self.debug_buffer is None:
+                self.debug_buffer = self.device.make_buffer(length=32)
+            cmd.set_buffer(self.debug_buffer, 0, L.INDEX_DEBUG)
+        cmd.set_params(params)
         cmd.dispatch_threads((self.width, self.rows, 1), (8, 8, 1))    # :137-141
         return cmd
 
@@ -88,6 +96,16 @@ class Renderer:
 
     def image(self):
         return self.render_buffer.contents(np.float32).reshape(self.rows, self.width, 4).copy()
+
+    def count_rays(self, **over):
+        """Render once with the counting variant; returns {paths, closest, shadow, shaded} (exact)."""
+        if self.debug_buffer is not None:
+            self.debug_buffer.contents(np.uint64)[:] = 0
+            self.debug_buffer.did_modify()
+        over["variant"] = over.get("variant", 0) | L.VARIANT_COUNT_RAYS
+        self.draw_async(**over).wait_until_completed()
+        c = self.debug_buffer.contents(np.uint64)
+        return dict(paths=int(c[0]), closest=int(c[1]), shadow=int(c[2]), shaded=int(c[3]))
 
     def clear(self):
         """Zero the accumulation target (progressive mode starts from 0)."""

@@ -74,6 +74,7 @@ enum {
 };
 
 enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
+enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_COUNT_RAYS = 0x100 };
 
 /* What the reference hard-codes in the shader (raytrace.metal:24-25,
  * shaders.metal:644,648) plus the tile / progressive controls BASELINE.json's
@@ -94,9 +95,14 @@ typedef struct RTLaunchParams {
     uint32_t numLights;        /* L (reference kernels read lights[0] only)          */
     uint32_t cameraRays;       /* drawTriangle: camera rays per pixel (reference: 6) */
     uint32_t misSamples;       /* drawTriangle: MIS samples, split in 3 (reference: 300) */
-    uint32_t variant;          /* 0 = tuned default; others select a kernel variant
-                                  for profiling                      */
-    uint32_t reserved[2];
+    uint32_t variant;          /* low byte: 0 = tuned default, else a kernel variant for profiling
+                                  (DESIGN.md).  RT_VARIANT_COUNT_RAYS (0x100): also add the exact
+                                  work counters {paths, closest rays, shadow rays, shaded bounces}
+                                  as 4 x uint64 to the buffer bound at RT_INDEX_DEBUG            */
+    uint32_t tileRows;         /* 0: the launch's rows are the contiguous global rows row0..row0+rows-1.
+                                  n > 0: interleaved row tiles for multi-GPU load balance: local row r
+                                  is global row  row0 + (r / n) * tileStride + (r % n)            */
+    uint32_t tileStride;       /* distance in rows between this launch's consecutive tiles (n * ranks) */
 } RTLaunchParams;
 
 typedef struct RTDeviceInfo {

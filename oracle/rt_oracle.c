@@ -233,8 +233,8 @@ static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint
 
 static int check_params(const RTLaunchParams *p) {
     if (!p) return RT_ERR_INVALID_ARGUMENT;
-    if (p->width <= 0 || p->height <= 0 || p->row0 < 0 || p->rows < 0 || p->row0 + p->rows > p->height)
-        return RT_ERR_INVALID_ARGUMENT;
+    if (p->width <= 0 || p->height <= 0 || p->row0 < 0 || p->rows < 0) return RT_ERR_INVALID_ARGUMENT;
+    if (!p->tileRows && p->row0 + p->rows > p->height) return RT_ERR_INVALID_ARGUMENT;
     return RT_OK;
 }
 
@@ -265,7 +265,9 @@ int rt_oracle_pathtrace(const CameraGPU *cameras, const MaterialGPU *materials,
         uint64_t cnt[RT_CNT_COUNT] = { 0 };
 #pragma omp for schedule(dynamic, 1)
         for (int ly = 0; ly < p->rows; ly++) {
-            const uint32_t iy = (uint32_t)(p->row0 + ly);
+            const uint32_t iy = p->tileRows
+                ? (uint32_t)p->row0 + ((uint32_t)ly / p->tileRows) * p->tileStride + ((uint32_t)ly % p->tileRows)
+                : (uint32_t)(p->row0 + ly);
             for (int x = 0; x < W; x++) {
                 const size_t px = (size_t)ly * W + x;
                 const uint32_t offset = offsets[px];          /* raytrace.metal:37 */

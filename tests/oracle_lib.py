@@ -18,7 +18,7 @@ class RTLaunchParams(C.Structure):
                 ("spp", C.c_uint32), ("firstSample", C.c_uint32), ("bounces", C.c_int32),
                 ("accumulate", C.c_int32), ("numTriangles", C.c_uint32), ("numSpheres", C.c_uint32),
                 ("numLights", C.c_uint32), ("cameraRays", C.c_uint32), ("misSamples", C.c_uint32),
-                ("variant", C.c_uint32), ("reserved", C.c_uint32 * 2)]
+                ("variant", C.c_uint32), ("tileRows", C.c_uint32), ("tileStride", C.c_uint32)]
 
 
 lib.rt_oracle_halton.restype = C.c_float
@@ -53,7 +53,7 @@ def offsets(width, row0, rows, seed=1):
 
 
 def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, bounces=3, accumulate=False,
-              out=None, off=None, seed=1, nthreads=0):
+              out=None, off=None, seed=1, nthreads=0, tile_rows=0, tile_stride=0):
     """Returns (image float32 [rows,width,4], counters uint64[8])."""
     rows = height - row0 if rows is None else rows
     if off is None:
@@ -62,7 +62,7 @@ def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, b
         out = np.zeros((rows, width, 4), np.float32)
     cnt = np.zeros(8, np.uint64)
     p = RTLaunchParams(width, height, row0, rows, spp, first_sample, bounces, int(accumulate),
-                       scene["T"], scene["S"], scene["L"], 6, 300, 0)
+                       scene["T"], scene["S"], scene["L"], 6, 300, 0, tile_rows, tile_stride)
     rc = lib.rt_oracle_pathtrace(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
                                  vp(scene["vertices"]), vp(scene["spheres"]), vp(off), vp(out), C.byref(p),
                                  vp(cnt), nthreads)

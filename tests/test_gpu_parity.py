@@ -162,3 +162,26 @@ def test_error_paths(dev):
     with pytest.raises(G.RTError) as e:
         G.Renderer(G.init_cornell_box(64, 64), 64, 64, device=dev, rows=32).encode(rows=64).commit()
     assert e.value.code in (-1, -5)
+
+
+def test_interleaved_tiles_and_exact_counters(dev):
+    """The multi-GPU deal on one GPU: every rank's interleaved rows, stitched, equal the full frame;
+    the counting variant reproduces the oracle's integer work counters exactly."""
+    from gpuraytracer_b200 import distributed as D
+    W, H, spp, world, tile = 208, 100, 4, 3, 8
+    sc = G.init_cornell_box(W, H)
+    ref, cnt = O.pathtrace(O.cornell(W, H), W, H, spp)
+    off_full = G.fill_offsets(W, 0, H).reshape(H, W)
+    idx, pad = D.scatter_index(H, world, tile)
+    parts = []
+    for rnk in range(world):
+        row0, rows, tr, ts = D.tile_params(H, rnk, world, tile)
+        mine = D.local_rows(H, rnk, world, tile)
+        r = G.Renderer(sc, W, H, device=dev, row0=row0, rows=rows, offsets=np.ascontiguousarray(off_full[mine]).reshape(-1))
+        img = r.draw(spp=spp, tileRows=tr, tileStride=ts)
+        parts.append(np.concatenate([img, np.zeros((pad - rows, W, 4), np.float32)]))
+    assert np.array_equal(np.concatenate(parts)[idx], ref)
+    r = G.Renderer(sc, W, H, device=dev)
+    c = r.count_rays(spp=spp)
+    assert [c["paths"], c["closest"], c["shadow"], c["shaded"]] == [int(v) for v in cnt[:4]]
+    assert np.array_equal(r.image(), ref)
