@@ -112,6 +112,66 @@ RT_INLINE float rt_cosf(float x) { float s, c; rt_sincosf(x, &s, &c); return c; 
 /* tan(x) = sin(x) / cos(x) */
 RT_INLINE float rt_tanf(float x) { float s, c; rt_sincosf(x, &s, &c); return s / c; }
 
+/* ---- <metal_stdlib> pow ----------------------------------------------------
+ * pow(x, y) = exp2(y * log2(x)), which is how a fast-math GPU library evaluates
+ * it (Sources/gpuRaytracer/shaders.metal:132-137,145-150,199-201,702-703 are the
+ * call sites).  log2: exponent/mantissa split with the mantissa in
+ * [sqrt(1/2), sqrt(2)), Cephes logf polynomial, one fma by log2(e).  exp2: split
+ * into integer and fraction in [-1/2, 1/2], Cephes exp2f polynomial, exponent
+ * added by bit arithmetic.  Exact special cases, as IEEE pow has them:
+ * pow(x, 1) = x, pow(x, 0) = 1, pow(1, y) = 1, pow(0, y > 0) = 0; x < 0 is NaN.
+ */
+RT_INLINE float rt_log2f(float x) {          /* x > 0, finite */
+    uint32_t bits; int e = 0;
+    if (x < 1.17549435e-38f) { x = x * 16777216.0f; e = -24; }
+    memcpy(&bits, &x, 4);
+    e += (int)((bits >> 23) & 0xffu) - 126;
+    bits = (bits & 0x007fffffu) | 0x3f000000u;           /* m in [0.5, 1) */
+    float m; memcpy(&m, &bits, 4);
+    if (m < 0.70710678118654752440f) { e -= 1; m = (m + m) - 1.0f; } else { m = m - 1.0f; }
+    float z = m * m;
+    float p = fmaf(7.0376836292e-2f, m, -1.1514610310e-1f);
+    p = fmaf(p, m, 1.1676998740e-1f);
+    p = fmaf(p, m, -1.2420140846e-1f);
+    p = fmaf(p, m, 1.4249322787e-1f);
+    p = fmaf(p, m, -1.6668057665e-1f);
+    p = fmaf(p, m, 2.0000714765e-1f);
+    p = fmaf(p, m, -2.4999993993e-1f);
+    p = fmaf(p, m, 3.3333331174e-1f);
+    float y = (p * m) * z;
+    y = fmaf(-0.5f, z, y);
+    float ln = m + y;
+    return fmaf(ln, 1.44269504088896341f, (float)e);
+}
+
+RT_INLINE float rt_exp2f(float t) {
+    if (!(t > -126.0f)) return 0.0f;                     /* underflow (and NaN) -> 0 */
+    if (t >= 128.0f) return INFINITY;
+    float nf = floorf(t + 0.5f);
+    float f = t - nf;                                     /* [-0.5, 0.5], exact */
+    float p = fmaf(1.535336188319500e-4f, f, 1.339887440266574e-3f);
+    p = fmaf(p, f, 9.618437357674640e-3f);
+    p = fmaf(p, f, 5.550332471162809e-2f);
+    p = fmaf(p, f, 2.402264791363012e-1f);
+    p = fmaf(p, f, 6.931472028550421e-1f);
+    p = fmaf(p, f, 1.0f);                                 /* 2^f in [0.707, 1.415] */
+    int n = (int)nf;
+    /* scale by 2^n in two exact steps so that n = 128 / -126 stay in range */
+    int n1 = n / 2, n2 = n - n1;
+    uint32_t b1 = (uint32_t)(n1 + 127) << 23, b2 = (uint32_t)(n2 + 127) << 23;
+    float s1, s2; memcpy(&s1, &b1, 4); memcpy(&s2, &b2, 4);
+    return (p * s1) * s2;
+}
+
+RT_INLINE float rt_powf(float x, float y) {
+    if (y == 1.0f) return x;
+    if (y == 0.0f || x == 1.0f) return 1.0f;
+    if (x == 0.0f) return y > 0.0f ? 0.0f : INFINITY;
+    if (!(x > 0.0f)) return NAN;
+    if (isinf(x)) return y > 0.0f ? INFINITY : 0.0f;
+    return rt_exp2f(y * rt_log2f(x));
+}
+
 /* ---- <metal_raytracing> intersector ---------------------------------------
  *
  * Replacement for the hardware BVH query: a brute-force loop over the T

@@ -1,0 +1,32 @@
+"""Generates the golden vectors in this directory from the reference's own shader source
+(oracle/_ref = RTrace/raytrace.metal + sampling.metal compiled as C++; needs /root/reference
+at build time).  Run from the repo root:  python tests/golden/make_golden.py
+Outputs (float32 / uint32, bit-exact expectations):
+  pathtrace_cornell_64x48_ref400spp.npz   image of the reference kernel at its literals
+                                          (400 spp, 3 bounces), offsets seed 3, + the inputs
+  halton_ref.npz                          halton(i, d) of sampling.metal:107-122 for 4096 (i, d)
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import oracle_lib as O   # noqa: E402  (fixtures only: scene bytes + offsets)
+import ref_lib as R      # noqa: E402
+
+ref = R.load()
+assert ref is not None, "oracle/_ref cannot be built here"
+W, H = 64, 48
+sc = O.cornell(W, H)
+off = O.offsets(W, 0, H, seed=3)
+img = R.pathtrace(ref, sc, W, H, off)
+np.savez_compressed(os.path.join(HERE, "pathtrace_cornell_64x48_ref400spp.npz"), image=img, offsets=off,
+                    camera=sc["camera"], materials=sc["materials"], lights=sc["lights"], vertices=sc["vertices"])
+rng = np.random.default_rng(11)
+i = np.concatenate([np.arange(64), rng.integers(0, 1 << 21, 4096 - 64 - 2), [0xffffffff, 1 << 24]]).astype(np.uint32)
+d = rng.integers(0, 24, i.size).astype(np.uint32)
+h = np.array([ref.rt_ref_halton(int(a), int(b)) for a, b in zip(i, d)], np.float32)
+np.savez_compressed(os.path.join(HERE, "halton_ref.npz"), i=i, d=d, value=h)
+print("wrote", os.listdir(HERE))
