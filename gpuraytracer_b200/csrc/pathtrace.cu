@@ -14,9 +14,9 @@
  *
  * Kernel shape (DESIGN.md has the numbers): one thread per pixel, a warp covers an
  * 8x4 pixel tile, a block 16x8 pixels.  Each block first stages the prepared scene
- * from HBM into shared memory; per sample the thread walks the bounce loop with the
- * Halton dimension fixed at compile time (the bounce loop is unrolled), and every
- * ray query is a loop over ALL primitives: there is no acceleration structure.
+ * from HBM into shared memory; per sample the thread walks the (rolled) bounce loop,
+ * and every ray query is a loop over ALL primitives: there is no acceleration
+ * structure.
  */
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -26,13 +26,10 @@
 
 using namespace rt;
 
-/* constant-bank copy of the intersection section (variant "const"): every lane
- * reads the same triangle, so the operands come through the uniform datapath and
- * cost neither LSU issue slots nor vector registers. */
-#define RT_CONST_TRIS 1024
-#define RT_CONST_SPHERES 1024
-__constant__ float4 c_isect[3 * RT_CONST_TRIS];
-__constant__ float4 c_sphere[RT_CONST_SPHERES];
+/* constant-bank mirror of the intersection part of the prepared scene (variant
+ * "const"): every lane reads the same primitive, so the operands come through the
+ * uniform datapath and cost neither LSU issue slots nor vector registers. */
+__constant__ float4 c_scene[RT_CONST_SLOTS];
 
 /* ------------------------------------------------------------------ prep ---- */
 struct SimdF3 { float x, y, z, pad; };
@@ -44,11 +41,11 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
                                          const unsigned char *__restrict__ spheres,
                                          float *__restrict__ scene, RTSceneLayout lay) {
     const int tid = threadIdx.x, nth = blockDim.x;
+    const float *cam = (const float *)camera;
+    const f3 position = mk(cam[0], cam[1], cam[2]);
     if (tid == 0) {
         /* generateCameraRay's per-launch part, sampling.metal:131-139 */
-        const float *cam = (const float *)camera;
         const int *cami = (const int *)camera;
-        f3 position = mk(cam[0], cam[1], cam[2]);
         f3 direction = mk(cam[4], cam[5], cam[6]);
         f3 up = mk(cam[8], cam[9], cam[10]);
         int resx = cami[12], resy = cami[13];
@@ -72,6 +69,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
     }
     for (uint32_t i = tid; i < lay.Tp; i += nth) {
         float *is = scene + lay.isect + RT_ISECT_WORDS * i;
+        float *ps = is + 12;
         float *sh = scene + lay.shade + i;
         if (i < lay.T) {
             const SimdF3 *vv = (const SimdF3 *)vertices + 3 * i;
@@ -79,10 +77,13 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             f3 v1 = mk(vv[1].x, vv[1].y, vv[1].z);
             f3 v2 = mk(vv[2].x, vv[2].y, vv[2].z);
             f3 e1 = v1 - v0, e2 = v2 - v0;
-            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = e1.x;
-            is[4] = e1.y; is[5] = e1.z; is[6] = e2.x; is[7] = e2.y;
-            is[8] = e2.z; is[9] = 0.0f; is[10] = 0.0f; is[11] = 0.0f;
-            f3 n = normalize(cross(e1, e2));                                 /* sampling.metal:16-26 */
+            f3 nn = cross(e1, e2);                 /* un-normalised: the intersector's n */
+            f3 w = v0 - position;                  /* camera rays: w and Nn do not depend on the ray */
+            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = nn.x;
+            is[4] = nn.y; is[5] = nn.z; is[6] = e2.x; is[7] = e2.y;
+            is[8] = e2.z; is[9] = -e1.x; is[10] = -e1.y; is[11] = -e1.z;
+            ps[0] = w.x; ps[1] = w.y; ps[2] = w.z; ps[3] = dot(w, nn);
+            f3 n = normalize(nn);                                            /* sampling.metal:16-26 */
             f3 right = normalize(cross(n, mk(0.0072f, 1.0f, 0.0034f)));      /* sampling.metal:57   */
             f3 fwd = cross(right, n);                                        /* sampling.metal:61   */
             const float *m = (const float *)(materials + 48 * (size_t)i);
@@ -96,17 +97,20 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             sh[RT_SH_METAL * lay.Tp] = m[4];
             sh[RT_SH_ROUGH * lay.Tp] = m[5];
         } else {
-            /* padding triangles are degenerate (all zero): det == 0, never accepted */
+            /* padding triangles are degenerate (all zero): D == 0, never accepted */
             for (int k = 0; k < RT_ISECT_WORDS; k++) is[k] = 0.0f;
             for (int k = 0; k < RT_SHADE_ROWS; k++) sh[k * lay.Tp] = 0.0f;
         }
     }
     for (uint32_t j = tid; j < lay.Sp; j += nth) {
-        float *sp = scene + lay.sphere + 4 * j;
+        float *sp = scene + lay.sphere + RT_SPHERE_WORDS * j;
+        float *pp = sp + 4;
         float *sh = scene + lay.sshade + j;
         if (j < lay.S) {
             const float *s = (const float *)(spheres + 80 * (size_t)j);   /* SphereGPU: center@0 material@16 radius@64 */
             sp[0] = s[0]; sp[1] = s[1]; sp[2] = s[2]; sp[3] = s[16];
+            f3 m = position - mk(s[0], s[1], s[2]);
+            pp[0] = m.x; pp[1] = m.y; pp[2] = m.z; pp[3] = fmaf(-s[16], s[16], dot(m, m));
             f3 em = mk(s[12], s[13], s[14]);
             sh[(RT_SSH_DR + 0) * lay.Sp] = s[4]; sh[(RT_SSH_DR + 1) * lay.Sp] = s[5]; sh[(RT_SSH_DR + 2) * lay.Sp] = s[6];
             sh[(RT_SSH_ER + 0) * lay.Sp] = em.x; sh[(RT_SSH_ER + 1) * lay.Sp] = em.y; sh[(RT_SSH_ER + 2) * lay.Sp] = em.z;
@@ -114,6 +118,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         } else {
             /* padding sphere: radius 0 far away; C > 0 and disc < 0 for any finite ray */
             sp[0] = 0.0f; sp[1] = 3.0e18f; sp[2] = 0.0f; sp[3] = 0.0f;
+            pp[0] = 0.0f; pp[1] = -3.0e18f; pp[2] = 0.0f; pp[3] = 9.0e36f;
             for (int k = 0; k < RT_SSHADE_ROWS; k++) sh[k * lay.Sp] = 0.0f;
         }
     }
@@ -127,78 +132,116 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
 
 /* ------------------------------------------------------------- intersector ---- */
 /*
- * Division-free Moller-Trumbore in the scaled form fixed by the arithmetic
- * contract: with p = cross(d,e2), det = dot(e1,p), tv = o - v0,
- * U = dot(tv,p), q = cross(tv,e1), V = dot(d,q), N = dot(e2,q), everything
- * multiplied by sign(det) and a = |det|, a hit needs
- *     U >= 0, V >= 0, U + V <= a, N >= tmin*a, N*bestD < bestN*a.
+ * Division-free ray/triangle test in the form fixed by the arithmetic contract
+ * (oracle/rt_detmath.h states the same thing for the CPU): with the
+ * per-triangle constants n = cross(e1,e2), e2, e1n = -e1 and, per ray,
+ *     w = v0 - o, D = dot(d,n), Nn = dot(w,n), c = cross(w,d), U = dot(e2,c), V = dot(e1n,c),
+ * everything multiplied by sign(D) and a = |D|, a hit needs
+ *     U >= 0, V >= 0, U + V <= a, Nn >= tmin*a, Nn*bestD < bestN*a.
  * (bestN,bestD) starts at (tmax,1).  One division, bestN/bestD, after the loop.
+ * 21 FP32 instructions + the comparisons; for camera rays w and Nn come from the
+ * prepared scene (they depend on the camera position only), leaving 15.
  */
-struct Best { float N, D; uint32_t id; };
-
-__device__ __forceinline__ bool tri_test(float4 A, float4 B, float4 C, f3 o, f3 d, float tmin,
-                                         float bestN, float bestD, float &N_out, float &a_out) {
-    f3 v0 = mk(A.x, A.y, A.z), e1 = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x);
-    f3 p = cross(d, e2);
-    float det = dot(e1, p);
-    f3 tv = o - v0;
-    float U = dot(tv, p);
-    f3 q = cross(tv, e1);
-    float V = dot(d, q);
-    float N = dot(e2, q);
-    uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+__device__ __forceinline__ bool tri_accept(float D, float Nn, float U, float V, float tmin,
+                                           float bestN, float bestD, float &N_out, float &a_out) {
+    uint32_t sgn = __float_as_uint(D) & 0x80000000u;
     U = __uint_as_float(__float_as_uint(U) ^ sgn);
     V = __uint_as_float(__float_as_uint(V) ^ sgn);
-    N = __uint_as_float(__float_as_uint(N) ^ sgn);
-    float a = fabsf(det);
-    N_out = N; a_out = a;
-    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & (N >= tmin * a) & (N * bestD < bestN * a);
+    Nn = __uint_as_float(__float_as_uint(Nn) ^ sgn);
+    float a = fabsf(D);
+    N_out = Nn; a_out = a;
+    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & (Nn >= tmin * a) & (Nn * bestD < bestN * a);
+}
+
+/* A = v0.xyz n.x | B = n.yz e2.xy | C = e2.z e1n.xyz */
+__device__ __forceinline__ bool tri_test(float4 A, float4 B, float4 C, f3 o, f3 d, float tmin,
+                                         float bestN, float bestD, float &N_out, float &a_out) {
+    f3 v0 = mk(A.x, A.y, A.z), n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+    f3 w = v0 - o;
+    float D = dot(d, n);
+    float Nn = dot(w, n);
+    f3 c = cross(w, d);
+    float U = dot(e2, c);
+    float V = dot(e1n, c);
+    return tri_accept(D, Nn, U, V, tmin, bestN, bestD, N_out, a_out);
+}
+
+/* camera ray: P = w.xyz Nn (prepared) */
+__device__ __forceinline__ bool tri_test_primary(float4 P, float4 A, float4 B, float4 C, f3 d, float tmin,
+                                                 float bestN, float bestD, float &N_out, float &a_out) {
+    f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+    f3 w = mk(P.x, P.y, P.z);
+    float D = dot(d, n);
+    f3 c = cross(w, d);
+    float U = dot(e2, c);
+    float V = dot(e1n, c);
+    return tri_accept(D, P.w, U, V, tmin, bestN, bestD, N_out, a_out);
 }
 
 /* sphere: m = o - c, A = d.d, B = m.d, C = m.m - r*r, disc = B*B - A*C, roots
  * (-B -+ sqrt(disc)) / A, nearer root first (rt_detmath.h: rt_sphere_test). */
-__device__ __forceinline__ bool sphere_test(float4 S, f3 o, f3 d, float tmin,
-                                            float bestN, float bestD, float &N_out, float &a_out) {
-    f3 m = o - mk(S.x, S.y, S.z);
-    float A = dot(d, d);
+__device__ __forceinline__ bool sphere_accept(f3 m, float C, float A, f3 d, float tmin,
+                                              float bestN, float bestD, float &N_out) {
     float B = dot(m, d);
-    float C = fmaf(-S.w, S.w, dot(m, m));
     float disc = fmaf(B, B, -(A * C));
     float sq = sqrtf(fmaxf(disc, 0.0f));
     bool real = disc >= 0.0f;
     float N0 = -B - sq, N1 = -B + sq;
     bool ok0 = real & (N0 >= tmin * A) & (N0 * bestD < bestN * A);
     bool ok1 = real & (N1 >= tmin * A) & (N1 * bestD < bestN * A);
-    N_out = ok0 ? N0 : N1; a_out = A;
+    N_out = ok0 ? N0 : N1;
     return ok0 | ok1;
 }
 
+/* The intersection part of the prepared scene, as float4 slots counted from the
+ * start of the isect section: triangle i = slots 4i..4i+3, sphere j = slots
+ * sph+2j, sph+2j+1.  CONST_BANK reads the constant-bank mirror, otherwise shared memory. */
 template <bool CONST_BANK>
 struct SceneRef {
-    const float4 *tri;      /* shared memory (or unused) */
-    const float4 *sph;
-    uint32_t T, S;
-    __device__ __forceinline__ float4 triA(uint32_t i, int k) const { return CONST_BANK ? c_isect[3 * i + k] : tri[3 * i + k]; }
-    __device__ __forceinline__ float4 sphere(uint32_t j) const { return CONST_BANK ? c_sphere[j] : sph[j]; }
+    const float4 *base;
+    uint32_t T, S;               /* PADDED loop bounds: T rounded up to 4, S to 2 */
+    uint32_t Treal, sph;
+    __device__ __forceinline__ float4 ld(uint32_t slot) const { return CONST_BANK ? c_scene[slot] : base[slot]; }
 };
 
-template <bool CONST_BANK>
+/* Both loops run over the PADDED counts T4 = T rounded up to 4 and S2 = S rounded up
+ * to 2 (the prepared scene pads with primitives that can never be accepted), so the
+ * unrolled bodies need no remainder code: less SASS, same results. */
+template <bool CONST_BANK, bool PRIMARY>
 __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax,
                                             float &dist, uint32_t &id) {
     float bestN = tmax, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
-#pragma unroll 4
-    for (uint32_t i = 0; i < sc.T; i++) {
-        float N, a;
-        if (tri_test(sc.triA(i, 0), sc.triA(i, 1), sc.triA(i, 2), o, d, tmin, bestN, bestD, N, a)) {
-            bestN = N; bestD = a; best = i;
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += 4) {
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++) {
+            const uint32_t i = i0 + u;
+            float N, a;
+            bool hit = PRIMARY ? tri_test_primary(sc.ld(4 * i + 3), sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), d, tmin, bestN, bestD, N, a)
+                               : tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, bestN, bestD, N, a);
+            if (hit) { bestN = N; bestD = a; best = i; }
         }
     }
-#pragma unroll 2
-    for (uint32_t j = 0; j < sc.S; j++) {
-        float N, a;
-        if (sphere_test(sc.sphere(j), o, d, tmin, bestN, bestD, N, a)) {
-            bestN = N; bestD = a; best = sc.T + j;
+    if (sc.S) {
+        const float A = dot(d, d);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                const uint32_t j = j0 + u;
+                float N;
+                bool hit;
+                if (PRIMARY) {
+                    float4 P = sc.ld(sc.sph + 2 * j + 1);
+                    hit = sphere_accept(mk(P.x, P.y, P.z), P.w, A, d, tmin, bestN, bestD, N);
+                } else {
+                    float4 Sp = sc.ld(sc.sph + 2 * j);
+                    f3 m = o - mk(Sp.x, Sp.y, Sp.z);
+                    hit = sphere_accept(m, fmaf(-Sp.w, Sp.w, dot(m, m)), A, d, tmin, bestN, bestD, N);
+                }
+                if (hit) { bestN = N; bestD = A; best = sc.Treal + j; }
+            }
         }
     }
     id = best;
@@ -209,15 +252,27 @@ __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o
 template <bool CONST_BANK>
 __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax) {
     bool hit = false;
-#pragma unroll 4
-    for (uint32_t i = 0; i < sc.T; i++) {
-        float N, a;
-        hit |= tri_test(sc.triA(i, 0), sc.triA(i, 1), sc.triA(i, 2), o, d, tmin, tmax, 1.0f, N, a);
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += 4) {
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++) {
+            const uint32_t i = i0 + u;
+            float N, a;
+            hit |= tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, tmax, 1.0f, N, a);
+        }
     }
-#pragma unroll 2
-    for (uint32_t j = 0; j < sc.S; j++) {
-        float N, a;
-        hit |= sphere_test(sc.sphere(j), o, d, tmin, tmax, 1.0f, N, a);
+    if (sc.S) {
+        const float A = dot(d, d);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                float N;
+                float4 Sp = sc.ld(sc.sph + 2 * (j0 + u));
+                f3 m = o - mk(Sp.x, Sp.y, Sp.z);
+                hit |= sphere_accept(m, fmaf(-Sp.w, Sp.w, dot(m, m)), A, d, tmin, tmax, 1.0f, N);
+            }
+        }
     }
     return hit;
 }
@@ -257,72 +312,18 @@ __device__ __forceinline__ f3 sample_cosine_hemisphere(float ux, float uy) {
 #define RT_BLOCK_H 8
 #define RT_BLOCK_THREADS 128
 
-template <int B>
-struct HaltonDims {
-    __device__ static __forceinline__ void light(uint32_t i, float &a, float &b) { a = halton<2 + 5 * B>(i); b = halton<3 + 5 * B>(i); }
-    __device__ static __forceinline__ void bsdf(uint32_t i, float &a, float &b) { a = halton<4 + 5 * B>(i); b = halton<5 + 5 * B>(i); }
-};
-
-/* one bounce of raytrace.metal:47-101; returns false when the path ends */
 struct Counters { uint32_t closest, shadow, shaded; };
 
-template <bool CONST_BANK, int B, bool COUNT>
-__device__ __forceinline__ bool bounce_step(const SceneRef<CONST_BANK> &sc, const float *__restrict__ sm,
-                                            const RTSceneLayout &lay, uint32_t numLights, uint32_t i,
-                                            f3 &ro, f3 &rd, f3 &color, f3 &acc, Counters &cnt) {
-    float dist; uint32_t id;
-    if (COUNT) cnt.closest++;
-    if (!closest_hit<CONST_BANK>(sc, ro, rd, 0.001f, 1000.0f, dist, id)) return false;     /* :51-53 */
-
-    f3 normal, right, fwd, diffuse;
-    if (id < lay.T) {
-        const float *sh = sm + lay.shade + id;
-        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                              /* :57-60 */
-            acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
-            return false;
-        }
-        normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
-        right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
-        fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
-        diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
-    } else {
-        uint32_t j = id - lay.T;
-        const float *sh = sm + lay.sshade + j;
-        if (sh[RT_SSH_FLAG * lay.Sp] != 0.0f) {
-            acc = mk(sh[(RT_SSH_ER + 0) * lay.Sp], sh[(RT_SSH_ER + 1) * lay.Sp], sh[(RT_SSH_ER + 2) * lay.Sp]);
-            return false;
-        }
-        float4 S = sc.sphere(j);
-        f3 hp = ro + rd * dist;
-        normal = normalize(hp - mk(S.x, S.y, S.z));
-        right = normalize(cross(normal, mk(0.0072f, 1.0f, 0.0034f)));
-        fwd = cross(right, normal);
-        diffuse = mk(sh[(RT_SSH_DR + 0) * lay.Sp], sh[(RT_SSH_DR + 1) * lay.Sp], sh[(RT_SSH_DR + 2) * lay.Sp]);
-    }
-    f3 P = (ro + rd * dist) + normal * 1e-3f;                                               /* :67 */
-    if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
-
-    float wx, wy;
-    HaltonDims<B>::light(i, wx, wy);                                                        /* :72-73 */
-    color = color * diffuse;                                                                /* :76 */
-    for (uint32_t l = 0; l < numLights; l++) {
-        const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
-        f3 ldir; float ldist;
-        f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
-        lightColor = lightColor * saturate(dot(normal, ldir));                              /* :75 */
-        /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
-        if (!any_hit<CONST_BANK>(sc, P, ldir, 0.0f, ldist - 1e-3f))
-            acc = acc + lightColor * color;                                                 /* :88 */
-    }
-    float ux, uy;
-    HaltonDims<B>::bsdf(i, ux, uy);                                                         /* :93-94 */
-    f3 s = sample_cosine_hemisphere(ux, uy);
-    f3 sd = (right * s.x + normal * s.y) + fwd * s.z;                                       /* sampling.metal:65 */
-    ro = P;                                                                                 /* :99-100 */
-    rd = sd;
-    return true;
-}
-
+/*
+ * One thread per pixel; the sample loop and the bounce loop are both ROLLED: the
+ * whole kernel is ~25 KB of SASS and its two primitive loops fit the 6 KB L0
+ * instruction cache (profiles/: the first version unrolled the bounces to get
+ * compile-time Halton bases, was 112 KB, and stalled on instruction fetch).
+ * The bounce index is warp-uniform (lanes whose path ended are merely inactive),
+ * so the Halton base of bounce b comes out of a constant table through the
+ * uniform datapath (halton_slot).  Bounce 0 uses the camera-ray form of the
+ * triangle test.
+ */
 template <bool CONST_BANK, bool COUNT>
 __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                float4 *__restrict__ out, const RTLaunchParams p,
@@ -348,9 +349,9 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
     const size_t pix = (size_t)ly * (uint32_t)p.width + x;
 
     SceneRef<CONST_BANK> sc;
-    sc.tri = (const float4 *)(sm + lay.isect);
-    sc.sph = (const float4 *)(sm + lay.sphere);
-    sc.T = lay.T; sc.S = lay.S;
+    sc.base = (const float4 *)(sm + lay.isect);
+    sc.T = (lay.T + 3u) & ~3u; sc.S = (lay.S + 1u) & ~1u; sc.Treal = lay.T;
+    sc.sph = 4 * lay.Tp;
 
     const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
     const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);
@@ -361,10 +362,12 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
     const float fx = (float)(int)x, fy = (float)(int)y;
 
     const uint32_t offset = offsets[pix];                               /* raytrace.metal:37, hoisted */
+    const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
     Counters cnt = { 0u, 0u, 0u };
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (p.accumulate) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 
+#pragma unroll 1
     for (uint32_t k = 0; k < p.spp; k++) {
         const uint32_t i = offset + (p.firstSample + k);
         /* camera ray, sampling.metal:141-147 */
@@ -376,13 +379,59 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
 
         f3 acc = mk(0.0f, 0.0f, 0.0f);
         f3 color = mk(1.0f, 1.0f, 1.0f);
-        const int nb = p.bounces;
-        do {
-            if (!bounce_step<CONST_BANK, 0, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 2) break;
-            if (!bounce_step<CONST_BANK, 1, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 3) break;
-            if (!bounce_step<CONST_BANK, 2, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt) || nb < 4) break;
-            bounce_step<CONST_BANK, 3, COUNT>(sc, sm, lay, p.numLights, i, ro, rd, color, acc, cnt);
-        } while (0);
+        float dist; uint32_t id;
+        if (COUNT) cnt.closest++;
+        bool hit = closest_hit<CONST_BANK, true>(sc, ro, rd, 0.001f, 1000.0f, dist, id);
+
+#pragma unroll 1
+        for (uint32_t b = 0; hit; b++) {                                                        /* raytrace.metal:47-101 */
+            f3 normal, right, fwd, diffuse;
+            if (id < lay.T) {
+                const float *sh = sm + lay.shade + id;
+                if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                          /* :57-60 */
+                    acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
+                    break;
+                }
+                normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
+                fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
+                diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
+            } else {
+                uint32_t j = id - lay.T;
+                const float *sh = sm + lay.sshade + j;
+                if (sh[RT_SSH_FLAG * lay.Sp] != 0.0f) {
+                    acc = mk(sh[(RT_SSH_ER + 0) * lay.Sp], sh[(RT_SSH_ER + 1) * lay.Sp], sh[(RT_SSH_ER + 2) * lay.Sp]);
+                    break;
+                }
+                const float *S = sm + lay.sphere + RT_SPHERE_WORDS * j;
+                f3 hp = ro + rd * dist;
+                normal = normalize(hp - mk(S[0], S[1], S[2]));
+                right = normalize(cross(normal, mk(0.0072f, 1.0f, 0.0034f)));
+                fwd = cross(right, normal);
+                diffuse = mk(sh[(RT_SSH_DR + 0) * lay.Sp], sh[(RT_SSH_DR + 1) * lay.Sp], sh[(RT_SSH_DR + 2) * lay.Sp]);
+            }
+            f3 P = (ro + rd * dist) + normal * 1e-3f;                                           /* :67 */
+            if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
+
+            float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                         /* :72-73 */
+            color = color * diffuse;                                                            /* :76 */
+            for (uint32_t l = 0; l < numLights; l++) {
+                const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
+                f3 ldir; float ldist;
+                f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+                lightColor = lightColor * saturate(dot(normal, ldir));                          /* :75 */
+                /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
+                if (!any_hit<CONST_BANK>(sc, P, ldir, 0.0f, ldist - 1e-3f))
+                    acc = acc + lightColor * color;                                             /* :88 */
+            }
+            if (b + 1 >= nb) break;
+            float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);                         /* :93-94 */
+            f3 sdir = sample_cosine_hemisphere(ux, uy);
+            rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                             /* sampling.metal:65 */
+            ro = P;                                                                             /* :99-100 */
+            if (COUNT) cnt.closest++;
+            hit = closest_hit<CONST_BANK, false>(sc, ro, rd, 0.001f, 1000.0f, dist, id);        /* :49 */
+        }
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
 
@@ -441,7 +490,8 @@ extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar
 /* what: 0 halton(i,d) [in: u32 pairs]          -> float  (compile-time-base path)
  *       1 sincos(x)   [in: float]              -> float2
  *       2 hash(x)     [in: u32]                -> u32
- *       3 halton_rt(i,d)                       -> float  (generic loop)            */
+ *       3 halton_rt(i,d)                       -> float  (generic loop)
+ *       4 halton_slot<s>(i,b), in: (i, 4*b+s)  -> float  (the path tracer's table-driven form) */
 template <int D>
 __device__ float halton_dispatch(uint32_t i, uint32_t d) {
     if (d == D) return halton<D>(i);
@@ -463,5 +513,10 @@ extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, 
     } else if (what == 3) {
         const uint32_t *p = (const uint32_t *)in;
         ((float *)out)[k] = halton_rt(p[2 * k], p[2 * k + 1]);
+    } else if (what == 4) {
+        const uint32_t *p = (const uint32_t *)in;
+        const uint32_t i = p[2 * k], b = p[2 * k + 1] >> 2, sl = p[2 * k + 1] & 3u;
+        float r = sl == 0 ? halton_slot<0>(i, b) : sl == 1 ? halton_slot<1>(i, b) : sl == 2 ? halton_slot<2>(i, b) : halton_slot<3>(i, b);
+        ((float *)out)[k] = r;
     }
 }

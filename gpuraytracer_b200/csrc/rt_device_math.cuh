@@ -116,11 +116,57 @@ __device__ __forceinline__ float halton(uint32_t i) {
     return r;
 }
 
+/* ---- Halton with a warp-uniform run-time dimension ------------------------------
+ * The path tracer's bounce loop is rolled, so the dimension 2 + 5*bounce + SLOT is a
+ * run-time value, but the same for every active lane of the warp.  Base, magic
+ * multiplier and the f_k products come out of a constant-bank table through the
+ * uniform datapath; the digit count is fixed per SLOT at compile time (the largest
+ * any bounce needs: extra digits are zero and add +0).  Digits: q = umulhi(i, M)
+ * with M = ceil(2^32 / B) is floor(i / B) exactly for i < 2^32 / B (error term
+ * i * (M*B - 2^32) < 2^32 needs i < 2^32 / 89), far above the 2^22 fast-path bound.
+ */
+#define RT_HAL_COLS 16
+struct HaltonTable {
+    float    f[24][RT_HAL_COLS];     /* f[d][k] = invB^(k+1), rounded after every product */
+    uint32_t B[24], M[24];
+};
+__host__ __device__ constexpr HaltonTable rt_make_halton_table() {
+    HaltonTable t{};
+    for (int d = 0; d < 24; d++) {
+        uint32_t b = rt_prime(d);
+        t.B[d] = b;
+        t.M[d] = (uint32_t)(((1ull << 32) + b - 1) / b);
+        for (int k = 0; k < RT_HAL_COLS; k++) t.f[d][k] = rt_halton_f(b, k);
+    }
+    return t;
+}
+__constant__ HaltonTable c_halton = rt_make_halton_table();
+
+__device__ __noinline__ float halton_rt(uint32_t i, uint32_t d);
+
+/* SLOT 0..3 of bounce b: dimension 2 + 5*b + SLOT (raytrace.metal:72-73,93-94) */
+template <int SLOT>
+__device__ __forceinline__ float halton_slot(uint32_t i, uint32_t bounce) {
+    /* digits needed for i < 2^22 in the smallest base the slot ever sees (bounce 0) */
+    constexpr int DIGITS = rt_digits_for(rt_prime(2 + SLOT), 1ull << 22);
+    static_assert(DIGITS <= RT_HAL_COLS, "table too narrow");
+    const uint32_t dim = 2u + 5u * bounce + (uint32_t)SLOT;
+    if (i >= (1u << 22)) return halton_rt(i, dim);
+    const uint32_t B = c_halton.B[dim], M = c_halton.M[dim];
+    float r = 0.0f;
+#pragma unroll
+    for (int k = 0; k < DIGITS; k++) {
+        uint32_t q = __umulhi(i, M);
+        uint32_t dgt = i - q * B;
+        r = r + c_halton.f[dim][k] * (float)dgt;
+        i = q;
+    }
+    return r;
+}
+
 /* run-time dimension (self-test and mode B) */
 __device__ __noinline__ float halton_rt(uint32_t i, uint32_t d) {
-    const uint32_t P[24] = { 2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37,
-                             41, 43, 47, 53, 59, 61, 67, 71, 73, 79, 83, 89 };
-    uint32_t b = P[d];
+    uint32_t b = c_halton.B[d];
     float f = 1.0f, invB = 1.0f / (float)b, r = 0.0f;
     while (i > 0) { f = f * invB; r = r + f * (float)(i % b); i = i / b; }
     return r;

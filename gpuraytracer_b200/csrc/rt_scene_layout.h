@@ -7,12 +7,18 @@
  * All sections are arrays of 32-bit words inside one flat buffer:
  *
  *   [0, RT_HDR_WORDS)               header: camera frame + counts   (floats / uints)
- *   isect  : 12 words per triangle  v0.xyz e1.x | e1.yz e2.xy | e2.z 0 0 0
- *            read with the SAME index by all lanes -> 3 broadcast 128-bit loads
+ *   --- intersection part (mirrored into the constant bank by the "const" variant) ---
+ *   isect  : 16 words per triangle  v0.xyz n.x | n.yz e2.xy | e2.z e1n.xyz | w.xyz Nn
+ *            e1n = v0 - v1, e2 = v2 - v0, n = cross(v1 - v0, e2)  (not normalised);
+ *            w = v0 - camera.position, Nn = dot(w, n): the ray-independent part of
+ *            the test for CAMERA rays, which read slots 1..3 (v0 is inside w);
+ *            read with the SAME index by all lanes -> broadcast 128-bit loads
+ *   sphere : 8 words per sphere     center.xyz radius | m.xyz C
+ *            m = camera.position - center, C = dot(m,m) - r*r (camera rays)
+ *   --- shading part ---
  *   shade  : RT_SHADE_ROWS rows of Tp words (structure of arrays, Tp = T rounded
  *            up to 32): looked up with the per-lane primitive id after a hit,
  *            so SoA keeps different ids on different banks
- *   sphere : 4 words per sphere     center.xyz radius
  *   sshade : RT_SSHADE_ROWS rows of Sp words
  *   light  : 8 words per light      center.xyz 0 | color.xyz 0
  */
@@ -33,7 +39,8 @@
 #define RT_HDR_RES_Y     15   /* float(camera.resolution.y)                          */
 #define RT_HDR_EXPOSURE  16   /* mode B: 1 / (1.2 * 2^ev100)                         */
 
-#define RT_ISECT_WORDS   12
+#define RT_ISECT_WORDS   16
+#define RT_SPHERE_WORDS   8
 
 /* shade rows (per triangle) */
 #define RT_SH_NX          0   /* geometric normal, getTriangleNormal                 */
@@ -53,6 +60,8 @@
 
 #define RT_LIGHT_WORDS    8
 
+/* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
+#define RT_CONST_SLOTS   3584
 #define RT_MAX_TRIANGLES 1024
 #define RT_MAX_SPHERES   1024
 #define RT_MAX_LIGHTS    16
@@ -60,7 +69,8 @@
 typedef struct RTSceneLayout {
     uint32_t T, S, L;
     uint32_t Tp, Sp;          /* padded to a multiple of 32                          */
-    uint32_t isect, shade, sphere, sshade, light;   /* section starts, in words      */
+    uint32_t isect, sphere;                         /* intersection part, section starts in words */
+    uint32_t shade, sshade, light;                  /* shading part                               */
     uint32_t words;           /* total size                                          */
 } RTSceneLayout;
 
@@ -75,11 +85,11 @@ RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
     l.T = T; l.S = S; l.L = L;
     l.Tp = (T + 31u) & ~31u;
     l.Sp = (S + 31u) & ~31u;
-    l.isect  = RT_HDR_WORDS;
-    l.shade  = l.isect + RT_ISECT_WORDS * l.Tp;
-    l.sphere = l.shade + RT_SHADE_ROWS * l.Tp;
-    l.sshade = l.sphere + 4u * l.Sp;
-    l.light  = l.sshade + RT_SSHADE_ROWS * l.Sp;
+    l.isect   = RT_HDR_WORDS;
+    l.sphere  = l.isect + RT_ISECT_WORDS * l.Tp;
+    l.shade   = l.sphere + RT_SPHERE_WORDS * l.Sp;
+    l.sshade  = l.shade + RT_SHADE_ROWS * l.Tp;
+    l.light   = l.sshade + RT_SSHADE_ROWS * l.Sp;
     l.words  = l.light + RT_LIGHT_WORDS * L;
     l.words  = (l.words + 3u) & ~3u;
     return l;

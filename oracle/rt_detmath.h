@@ -178,23 +178,28 @@ RT_INLINE float rt_powf(float x, float y) {
  * triangles of the vertex buffer (stride 16 bytes, three vertices per
  * triangle, primitive_id = triangle index; reference
  * RTrace/computeShader.swift:47-66, RTrace/renderer.swift:51-57) with a
- * division-free Moller-Trumbore test.  For triangle (v0,v1,v2), ray (o,d):
+ * division-free ray/triangle test in the "precomputed normal" form of
+ * Moller-Trumbore.  Per triangle (v0,v1,v2), independent of the ray:
  *
- *     e1 = v1-v0   e2 = v2-v0
- *     p  = cross(d, e2)        det = dot(e1, p)
- *     tv = o - v0              U   = dot(tv, p)
- *     q  = cross(tv, e1)       V   = dot(d, q)        N = dot(e2, q)
- *     if det < 0 (sign bit set): U,V,N = -U,-V,-N ;   a = |det|
+ *     e1 = v1-v0   e2 = v2-v0   n = cross(e1, e2)   e1n = -e1
  *
- * (u,v,t) = (U,V,N)/a are never formed inside the loop.  The hit is accepted
- * when
+ * and per ray (o,d):
+ *
+ *     w  = v0 - o              D  = dot(d, n)         Nn = dot(w, n)
+ *     c  = cross(w, d)         U  = dot(e2, c)        V  = dot(e1n, c)
+ *     if D < 0 (sign bit set): U,V,Nn = -U,-V,-Nn ;   a = |D|
+ *
+ * which are the classic quantities scaled by the determinant: (u,v,t) =
+ * (U,V,Nn)/a, never formed inside the loop.  The hit is accepted when
  *     U >= 0  &&  V >= 0  &&  U+V <= a           inside, edges inclusive, no culling
- *     N >= tmin*a                                  t >= tmin
- *     N*bestD < bestN*a                            t <  best so far (strict)
+ *     Nn >= tmin*a                                 t >= tmin
+ *     Nn*bestD < bestN*a                           t <  best so far (strict)
  * where (bestN,bestD) starts as (tmax,1), so the same comparison enforces
  * t < tmax, and a tie between two triangles keeps the LOWER primitive id.
- * det == 0 can never pass (it would need N >= 0 and N < 0).  The reported
+ * D == 0 can never pass (it would need Nn >= 0 and Nn < 0).  The reported
  * distance is the single division bestN/bestD after the loop.
+ * Cost: 21 multiply/add instructions per test (w 3, D 3, Nn 3, c 6, U 3, V 3),
+ * 32 flop, + 4 flop for the comparisons' products and sum.
  *
  * accept_any_intersection(true) (shadow rays, raytrace.metal:83) answers only
  * hit / no hit; it is the same test and may stop at the first accepted
@@ -215,18 +220,18 @@ RT_INLINE int rt_triangle_test(const float *v0, const float *v1, const float *v2
                                float *bestN, float *bestD) {
     float e1x = v1[0] - v0[0], e1y = v1[1] - v0[1], e1z = v1[2] - v0[2];
     float e2x = v2[0] - v0[0], e2y = v2[1] - v0[1], e2z = v2[2] - v0[2];
-    float px, py, pz, qx, qy, qz;
-    rt_cross3(d[0], d[1], d[2], e2x, e2y, e2z, &px, &py, &pz);
-    float det = rt_dot3(e1x, e1y, e1z, px, py, pz);
-    float tx = o[0] - v0[0], ty = o[1] - v0[1], tz = o[2] - v0[2];
-    float U = rt_dot3(tx, ty, tz, px, py, pz);
-    rt_cross3(tx, ty, tz, e1x, e1y, e1z, &qx, &qy, &qz);
-    float V = rt_dot3(d[0], d[1], d[2], qx, qy, qz);
-    float N = rt_dot3(e2x, e2y, e2z, qx, qy, qz);
-    if (signbit(det)) { U = -U; V = -V; N = -N; }
-    float a = fabsf(det);
-    if (U >= 0.0f && V >= 0.0f && U + V <= a && N >= tmin * a && N * *bestD < *bestN * a) {
-        *bestN = N; *bestD = a;
+    float nx, ny, nz, cx, cy, cz;
+    rt_cross3(e1x, e1y, e1z, e2x, e2y, e2z, &nx, &ny, &nz);
+    float wx = v0[0] - o[0], wy = v0[1] - o[1], wz = v0[2] - o[2];
+    float D  = rt_dot3(d[0], d[1], d[2], nx, ny, nz);
+    float Nn = rt_dot3(wx, wy, wz, nx, ny, nz);
+    rt_cross3(wx, wy, wz, d[0], d[1], d[2], &cx, &cy, &cz);
+    float U = rt_dot3(e2x, e2y, e2z, cx, cy, cz);
+    float V = rt_dot3(-e1x, -e1y, -e1z, cx, cy, cz);
+    if (signbit(D)) { U = -U; V = -V; Nn = -Nn; }
+    float a = fabsf(D);
+    if (U >= 0.0f && V >= 0.0f && U + V <= a && Nn >= tmin * a && Nn * *bestD < *bestN * a) {
+        *bestN = Nn; *bestD = a;
         return 1;
     }
     return 0;

@@ -50,6 +50,19 @@ def test_halton_bit_exact(dev):
         assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), what
 
 
+def test_halton_slot_table_form_bit_exact(dev):
+    """halton_slot<s>(i, bounce): the table-driven form the rolled bounce loop uses (dimension 2+5b+s)."""
+    rng = np.random.default_rng(5)
+    n = 1 << 16
+    idx = rng.integers(0, (1 << 20) + 4096, n).astype(np.uint32)
+    idx[:8] = [0, 1, 2, 3, (1 << 22) - 1, 1 << 22, (1 << 24) + 5, 0xffffffff]
+    code = rng.integers(0, 16, n).astype(np.uint32)              # 4*bounce + slot
+    pairs = np.stack([idx, code], 1).copy()
+    ref = np.array([O.lib.rt_oracle_halton(int(i), 2 + 5 * (int(c) >> 2) + (int(c) & 3)) for i, c in pairs], np.float32)
+    got = debug_eval(dev, 4, pairs, np.zeros(n, np.float32))
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
 def test_sincos_and_hash_bit_exact(dev):
     x = np.concatenate([np.linspace(0, 6.2831855, 100000), np.random.default_rng(2).uniform(-50, 50, 31072)]).astype(np.float32)
     got = debug_eval(dev, 1, x, np.zeros((x.size, 2), np.float32))
