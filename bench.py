@@ -27,10 +27,11 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "Mpaths/s, Cornell 1080p x 1024spp"
+METRIC = "Mpaths/s, Cornell 1080p x 1024spp at 1/2/4/8 B200; % of FP32 peak"
 UNIT = "Mpaths/s"
 W, H = 1920, 1080
 TILE_ROWS = 8
+NCU_DRAM_BYTES_PER_LAUNCH = 8384000 + 3840      # profiles/r01b_ncu_full_pathTrace_smem_64spp.txt
 
 
 def parse():
@@ -227,7 +228,9 @@ def run_ours(a, rank, world, local_rank):
     frame_paths = W * H * a.spp
     assert paths == frame_paths, (paths, frame_paths)
     T = scene.num_triangles
-    flops = 45 * T * (closest + shadow) + 200 * shaded + 60 * paths
+    flops = 45 * T * (closest + shadow) + 200 * shaded + 60 * paths          # the contract figure
+    # what the kernel executes: 36 flop per triangle test (precomputed-normal form), 28 for camera rays
+    flops_exec = T * (28 * paths + 36 * (closest - paths + shadow)) + 200 * shaded + 60 * paths
     info = r.device.info()
     k_ms = sum(kernel_ms) / len(kernel_ms)                # this rank's prep+trace per step
     peak = info.smCount * 128 * 2 * (info.clockKHz * 1e3) / 1e12
@@ -241,7 +244,11 @@ def run_ours(a, rank, world, local_rank):
                    "h2d_bytes_per_step": int(h2d_t.item()), "d2h_bytes_per_step": W * H * 16},
            "gpu_launches": launches * world,
            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                        "traffic": None,
+                        "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
+                        "traffic_note": "dram__bytes_read+write of one pathTrace launch from the ncu --set full capture in "
+                                        "profiles/ (offsets read once; the 33 MB of output is still in L2 when the launch ends)",
+                        "executed_flops_frac": flops_exec * my_share / (k_ms * 1e-3) / 1e12 / peak,
+                        "executed_flops_per_path": flops_exec / paths,
                         "peak_kind": f"nominal {info.smCount} SMs x 128 lanes x 2 x {info.clockKHz / 1e3:.0f} MHz "
                                      "(MEASURED_PEAKS.json has no FP32 figure)",
                         "kernel": "pathTrace (prep + trace), rank 0", "kernel_ms": k_ms,

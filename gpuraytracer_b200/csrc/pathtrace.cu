@@ -207,15 +207,15 @@ struct SceneRef {
 /* Both loops run over the PADDED counts T4 = T rounded up to 4 and S2 = S rounded up
  * to 2 (the prepared scene pads with primitives that can never be accepted), so the
  * unrolled bodies need no remainder code: less SASS, same results. */
-template <bool CONST_BANK, bool PRIMARY>
+template <bool CONST_BANK, bool PRIMARY, int UNROLL>
 __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax,
                                             float &dist, uint32_t &id) {
     float bestN = tmax, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
 #pragma unroll 1
-    for (uint32_t i0 = 0; i0 < sc.T; i0 += 4) {
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
 #pragma unroll
-        for (uint32_t u = 0; u < 4; u++) {
+        for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
             float N, a;
             bool hit = PRIMARY ? tri_test_primary(sc.ld(4 * i + 3), sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), d, tmin, bestN, bestD, N, a)
@@ -249,13 +249,13 @@ __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o
     return best != 0xffffffffu;
 }
 
-template <bool CONST_BANK>
+template <bool CONST_BANK, int UNROLL>
 __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax) {
     bool hit = false;
 #pragma unroll 1
-    for (uint32_t i0 = 0; i0 < sc.T; i0 += 4) {
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
 #pragma unroll
-        for (uint32_t u = 0; u < 4; u++) {
+        for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
             float N, a;
             hit |= tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, tmax, 1.0f, N, a);
@@ -324,7 +324,7 @@ struct Counters { uint32_t closest, shadow, shaded; };
  * uniform datapath (halton_slot).  Bounce 0 uses the camera-ray form of the
  * triangle test.
  */
-template <bool CONST_BANK, bool COUNT>
+template <bool CONST_BANK, bool COUNT, int UNROLL>
 __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                float4 *__restrict__ out, const RTLaunchParams p,
                                                const RTSceneLayout lay, float *sm,
@@ -350,7 +350,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
 
     SceneRef<CONST_BANK> sc;
     sc.base = (const float4 *)(sm + lay.isect);
-    sc.T = (lay.T + 3u) & ~3u; sc.S = (lay.S + 1u) & ~1u; sc.Treal = lay.T;
+    sc.T = (lay.T + (UNROLL - 1)) / UNROLL * UNROLL; sc.S = (lay.S + 1u) & ~1u; sc.Treal = lay.T;
     sc.sph = 4 * lay.Tp;
 
     const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
@@ -381,7 +381,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
         f3 color = mk(1.0f, 1.0f, 1.0f);
         float dist; uint32_t id;
         if (COUNT) cnt.closest++;
-        bool hit = closest_hit<CONST_BANK, true>(sc, ro, rd, 0.001f, 1000.0f, dist, id);
+        bool hit = closest_hit<CONST_BANK, true, UNROLL>(sc, ro, rd, 0.001f, 1000.0f, dist, id);
 
 #pragma unroll 1
         for (uint32_t b = 0; hit; b++) {                                                        /* raytrace.metal:47-101 */
@@ -421,7 +421,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
                 f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));                          /* :75 */
                 /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
-                if (!any_hit<CONST_BANK>(sc, P, ldir, 0.0f, ldist - 1e-3f))
+                if (!any_hit<CONST_BANK, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f))
                     acc = acc + lightColor * color;                                             /* :88 */
             }
             if (b + 1 >= nb) break;
@@ -430,7 +430,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
             rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                             /* sampling.metal:65 */
             ro = P;                                                                             /* :99-100 */
             if (COUNT) cnt.closest++;
-            hit = closest_hit<CONST_BANK, false>(sc, ro, rd, 0.001f, 1000.0f, dist, id);        /* :49 */
+            hit = closest_hit<CONST_BANK, false, UNROLL>(sc, ro, rd, 0.001f, 1000.0f, dist, id);        /* :49 */
         }
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
@@ -451,17 +451,23 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
     }
 }
 
-#define RT_PATHTRACE_ENTRY(name, CONST_BANK, COUNT)                                                              \
-    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)                                            \
+#define RT_PATHTRACE_ENTRY(name, CONST_BANK, COUNT, UNROLL, MINB)                                                \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_body<CONST_BANK, COUNT>(scene, offsets, out, p, lay, sm, counters);                            \
+        pathtrace_body<CONST_BANK, COUNT, UNROLL>(scene, offsets, out, p, lay, sm, counters);                    \
     }
-RT_PATHTRACE_ENTRY(pathTrace_smem, false, false)
-RT_PATHTRACE_ENTRY(pathTrace_const, true, false)
-RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true)
-RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true)
+RT_PATHTRACE_ENTRY(pathTrace_smem, false, false, 4, 4)
+RT_PATHTRACE_ENTRY(pathTrace_const, true, false, 4, 4)
+RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true, 4, 4)
+RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
+/* tuning experiments (variant ids 3..): unroll x resident blocks per SM; the winner becomes pathTrace_smem */
+RT_PATHTRACE_ENTRY(pathTrace_exp3, false, false, 4, 5)
+RT_PATHTRACE_ENTRY(pathTrace_exp4, false, false, 2, 6)
+RT_PATHTRACE_ENTRY(pathTrace_exp5, false, false, 2, 8)
+RT_PATHTRACE_ENTRY(pathTrace_exp6, false, false, 4, 6)
+RT_PATHTRACE_ENTRY(pathTrace_exp7, false, false, 6, 3)
 
 /* ----------------------------------------------------------------- resolve ---- */
 /* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.
