@@ -4,6 +4,7 @@ at build time).  Run from the repo root:  python tests/golden/make_golden.py
 Outputs (float32 / uint32, bit-exact expectations):
   pathtrace_cornell_64x48_ref400spp.npz   image of the reference kernel at its literals
                                           (400 spp, 3 bounces), offsets seed 3, + the inputs
+  drawtriangle_cornell_64x48_ref.npz      RGBA8 + float3 buffers of the reference MIS kernel (6 x 300)
   halton_ref.npz                          halton(i, d) of sampling.metal:107-122 for 4096 (i, d)
 """
 import os
@@ -24,6 +25,11 @@ off = O.offsets(W, 0, H, seed=3)
 img = R.pathtrace(ref, sc, W, H, off)
 np.savez_compressed(os.path.join(HERE, "pathtrace_cornell_64x48_ref400spp.npz"), image=img, offsets=off,
                     camera=sc["camera"], materials=sc["materials"], lights=sc["lights"], vertices=sc["vertices"])
+# mode B: the reference MIS kernel at its literals (6 camera rays, 300 MIS samples), 1.5 x 1.5 light
+scb = O.cornell(W, H, light_size=1.5)
+pxb, txb = R.drawtriangle(ref, scb, W, H)
+np.savez_compressed(os.path.join(HERE, "drawtriangle_cornell_64x48_ref.npz"), pixels=pxb, text=txb,
+                    camera=scb["camera"], materials=scb["materials"], lights=scb["lights"], vertices=scb["vertices"])
 rng = np.random.default_rng(11)
 i = np.concatenate([np.arange(64), rng.integers(0, 1 << 21, 4096 - 64 - 2), [0xffffffff, 1 << 24]]).astype(np.uint32)
 d = rng.integers(0, 24, i.size).astype(np.uint32)

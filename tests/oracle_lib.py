@@ -71,6 +71,22 @@ def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, b
     return out, cnt
 
 
+def drawtriangle(scene, width, height, *, row0=0, rows=None, camera_rays=6, mis_samples=300, nthreads=0,
+                 tile_rows=0, tile_stride=0):
+    """Mode B (drawTriangle, MIS).  Returns (pixels uint8 [rows,width,4], text float32 [rows,width,3], counters)."""
+    rows = height - row0 if rows is None else rows
+    pixels = np.zeros((rows, width, 4), np.uint8)
+    text = np.zeros((rows, width, 3), np.float32)
+    cnt = np.zeros(8, np.uint64)
+    p = RTLaunchParams(width, height, row0, rows, 0, 0, 0, 0, scene["T"], 0, scene["L"], camera_rays, mis_samples,
+                       0, tile_rows, tile_stride)
+    rc = lib.rt_oracle_drawtriangle(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
+                                    vp(scene["vertices"]), vp(pixels), vp(text), C.byref(p), vp(cnt), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_drawtriangle returned {rc}")
+    return pixels, text, cnt
+
+
 def flops(cnt, T, S):
     """F = 45*T*(Rc+Rs) + 18*S*(Rc+Rs) + 200*B + 60*P."""
     P, Rc, Rs, B = (int(cnt[i]) for i in range(4))

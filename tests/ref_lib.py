@@ -36,3 +36,14 @@ def pathtrace(lib, scene, width, height, offsets, row0=0, rows=None):
                               C.c_uint32(scene["T"]), vp(offsets), vp(out), width, height, row0, rows)
     assert rc == 0
     return out[row0:row0 + rows]
+
+
+def drawtriangle(lib, scene, width, height, row0=0, rows=None):
+    """The reference MIS kernel at its own literals (6 camera rays, 300 MIS samples)."""
+    rows = height - row0 if rows is None else rows
+    pixels = np.zeros((height, width, 4), np.uint8)
+    text = np.zeros((height, width, 3), np.float32)
+    rc = lib.rt_ref_drawtriangle(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]), vp(scene["vertices"]),
+                                 C.c_uint32(scene["T"]), vp(pixels), vp(text), width, height, row0, rows)
+    assert rc == 0
+    return pixels[row0:row0 + rows], text[row0:row0 + rows]

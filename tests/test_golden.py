@@ -30,6 +30,16 @@ def test_oracle_pathtrace_matches_golden_image():
     assert np.array_equal(got.view(np.uint32), g["image"].view(np.uint32))
 
 
+def test_oracle_drawtriangle_matches_golden():
+    g = golden("drawtriangle_cornell_64x48_ref.npz")
+    sc = O.cornell(64, 48, light_size=1.5)
+    for k in ("camera", "materials", "lights", "vertices"):
+        assert np.array_equal(sc[k], g[k]), k
+    px, tx, _ = O.drawtriangle(sc, 64, 48)
+    assert np.array_equal(tx.view(np.uint32), g["text"].view(np.uint32))
+    assert np.array_equal(px, g["pixels"])
+
+
 @pytest.mark.gpu
 def test_gpu_pathtrace_matches_golden_image():
     import gpuraytracer_b200 as G

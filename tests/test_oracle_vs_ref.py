@@ -42,3 +42,29 @@ def test_reference_row_window_matches_full_frame():
     part = R.pathtrace(ref, sc, W, H, off, row0=20, rows=4)
     got, _ = O.pathtrace(sc, W, H, 400, row0=20, rows=4, off=off[20 * W:24 * W].copy())
     assert np.array_equal(got, part)
+
+
+# ---- mode B: drawTriangle (MIS), Sources/gpuRaytracer/shaders.metal ---------------------------
+def test_drawtriangle_restatement_is_bit_identical_to_reference_shader():
+    W, H = 64, 48
+    sc = O.cornell(W, H, light_size=1.5)          # Sources/gpuRaytracer/main.swift:30-31
+    want_px, want_tx = R.drawtriangle(ref, sc, W, H)
+    got_px, got_tx, cnt = O.drawtriangle(sc, W, H)   # defaults = the shader's literals: 6 rays, 300 MIS samples
+    assert int(cnt[0]) == W * H * 6
+    assert want_tx.max() > 1.0 and not np.isnan(want_tx).any()
+    assert np.array_equal(got_tx.view(np.uint32), want_tx.view(np.uint32)), f"{(got_tx != want_tx).sum()} values differ"
+    assert np.array_equal(got_px, want_px)
+
+
+def test_drawtriangle_4x3_aspect_and_hash_random():
+    """800x600-like aspect (the shader hard-codes 800/600 in hashRandom): a small 4:3 window, a few rows."""
+    import ctypes as C
+    W, H = 80, 60
+    sc = O.cornell(W, H, light_size=1.5)
+    want_px, want_tx = R.drawtriangle(ref, sc, W, H, row0=28, rows=3)
+    got_px, got_tx, _ = O.drawtriangle(sc, W, H, row0=28, rows=3)
+    assert np.array_equal(got_tx.view(np.uint32), want_tx.view(np.uint32))
+    assert np.array_equal(got_px, want_px)
+    out = (C.c_float * 2)()
+    ref.rt_ref_b_hash_random(5, 7, 3, out)
+    assert 0.0 <= out[0] <= 1.0 and 0.0 <= out[1] <= 1.0
