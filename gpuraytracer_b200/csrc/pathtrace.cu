@@ -64,7 +64,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         scene[RT_HDR_HALF_H] = halfHeight;
         scene[RT_HDR_RES_X] = (float)resx;
         scene[RT_HDR_RES_Y] = (float)resy;
-        scene[RT_HDR_EXPOSURE] = ev100;   /* mode B fills the real value */
+        scene[RT_HDR_EXPOSURE] = 1.0f / (1.2f * pow_det(2.0f, ev100));   /* cameraExposure, shaders.metal:145-150 */
         for (int i = RT_HDR_EXPOSURE + 1; i < RT_HDR_WORDS; i++) scene[i] = 0.0f;
     }
     for (uint32_t i = tid; i < lay.Tp; i += nth) {
@@ -96,6 +96,10 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             sh[RT_SH_FLAG * lay.Tp] = (length(em) > 0.0f) ? 1.0f : 0.0f;     /* raytrace.metal:57   */
             sh[RT_SH_METAL * lay.Tp] = m[4];
             sh[RT_SH_ROUGH * lay.Tp] = m[5];
+            f3 tg, bt;
+            orthonormal_basis(n, tg, bt);                                    /* shaders.metal:159-172 */
+            sh[(RT_SH_TX + 0) * lay.Tp] = tg.x; sh[(RT_SH_TX + 1) * lay.Tp] = tg.y; sh[(RT_SH_TX + 2) * lay.Tp] = tg.z;
+            sh[(RT_SH_BX + 0) * lay.Tp] = bt.x; sh[(RT_SH_BX + 1) * lay.Tp] = bt.y; sh[(RT_SH_BX + 2) * lay.Tp] = bt.z;
         } else {
             /* padding triangles are degenerate (all zero): D == 0, never accepted */
             for (int k = 0; k < RT_ISECT_WORDS; k++) is[k] = 0.0f;
@@ -127,6 +131,8 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         float *d = scene + lay.light + RT_LIGHT_WORDS * l;
         d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = 0.0f;
         d[4] = s[4]; d[5] = s[5]; d[6] = s[6]; d[7] = 0.0f;
+        d[8] = s[8]; d[9] = s[9]; d[10] = s[10]; d[11] = 0.0f;            /* emittedRadiance@32 */
+        d[12] = s[12]; d[13] = s[13]; d[14] = 0.0f; d[15] = 0.0f;         /* width@48 depth@52  */
     }
 }
 
@@ -468,6 +474,8 @@ RT_PATHTRACE_ENTRY(pathTrace_exp4, false, false, 2, 6)
 RT_PATHTRACE_ENTRY(pathTrace_exp5, false, false, 2, 8)
 RT_PATHTRACE_ENTRY(pathTrace_exp6, false, false, 4, 6)
 RT_PATHTRACE_ENTRY(pathTrace_exp7, false, false, 6, 3)
+
+#include "modeb.cuh"
 
 /* ----------------------------------------------------------------- resolve ---- */
 /* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.

@@ -27,6 +27,8 @@ __device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk(a.x - b.x, a.y -
 __device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ f3 operator*(f3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ f3 operator-(f3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ f3 operator/(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ f3 operator/(f3 a, f3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }
 
 /* ---- Metal stdlib stand-ins (fused where written) ---------------------------- */
 __device__ __forceinline__ float dot(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
@@ -61,6 +63,62 @@ __device__ __forceinline__ void sincos_det(float x, float &s_out, float &c_out) 
     c_out = ((k + 1) & 2) ? -cc : cc;
 }
 __device__ __forceinline__ float tan_det(float x) { float s, c; sincos_det(x, s, c); return s / c; }
+
+/* ---- pow = exp2(y * log2(x)): same split, polynomials and special cases on the CPU side
+ * of the arithmetic contract.  Call sites are mode B's:
+ * Sources/gpuRaytracer/shaders.metal:132-137,145-150,199-201,702-703. */
+__device__ __forceinline__ float log2_det(float x) {
+    int e = 0;
+    if (x < 1.17549435e-38f) { x = x * 16777216.0f; e = -24; }
+    uint32_t bits = __float_as_uint(x);
+    e += (int)((bits >> 23) & 0xffu) - 126;
+    float m = __uint_as_float((bits & 0x007fffffu) | 0x3f000000u);
+    if (m < 0.70710678118654752440f) { e -= 1; m = (m + m) - 1.0f; } else { m = m - 1.0f; }
+    float z = m * m;
+    float p = fmaf(7.0376836292e-2f, m, -1.1514610310e-1f);
+    p = fmaf(p, m, 1.1676998740e-1f);
+    p = fmaf(p, m, -1.2420140846e-1f);
+    p = fmaf(p, m, 1.4249322787e-1f);
+    p = fmaf(p, m, -1.6668057665e-1f);
+    p = fmaf(p, m, 2.0000714765e-1f);
+    p = fmaf(p, m, -2.4999993993e-1f);
+    p = fmaf(p, m, 3.3333331174e-1f);
+    float y = (p * m) * z;
+    y = fmaf(-0.5f, z, y);
+    float ln = m + y;
+    return fmaf(ln, 1.44269504088896341f, (float)e);
+}
+__device__ __forceinline__ float exp2_det(float t) {
+    if (!(t > -126.0f)) return 0.0f;
+    if (t >= 128.0f) return __int_as_float(0x7f800000);
+    float nf = floorf(t + 0.5f);
+    float f = t - nf;
+    float p = fmaf(1.535336188319500e-4f, f, 1.339887440266574e-3f);
+    p = fmaf(p, f, 9.618437357674640e-3f);
+    p = fmaf(p, f, 5.550332471162809e-2f);
+    p = fmaf(p, f, 2.402264791363012e-1f);
+    p = fmaf(p, f, 6.931472028550421e-1f);
+    p = fmaf(p, f, 1.0f);
+    int n = (int)nf;
+    int n1 = n / 2, n2 = n - n1;
+    float s1 = __uint_as_float((uint32_t)(n1 + 127) << 23), s2 = __uint_as_float((uint32_t)(n2 + 127) << 23);
+    return (p * s1) * s2;
+}
+__device__ __forceinline__ float pow_det(float x, float y) {
+    if (y == 1.0f) return x;
+    if (y == 0.0f || x == 1.0f) return 1.0f;
+    if (x == 0.0f) return y > 0.0f ? 0.0f : __int_as_float(0x7f800000);
+    if (!(x > 0.0f)) return __int_as_float(0x7fc00000);
+    if (isinf(x)) return y > 0.0f ? __int_as_float(0x7f800000) : 0.0f;
+    return exp2_det(y * log2_det(x));
+}
+
+/* buildOrthonormalBasis, Sources/gpuRaytracer/shaders.metal:159-172 */
+__device__ __forceinline__ void orthonormal_basis(f3 normal, f3 &tangent, f3 &bitangent) {
+    if (fabsf(normal.x) > 0.9f) tangent = normalize(mk(0.0f, 1.0f, 0.0f) - normal * dot(mk(0.0f, 1.0f, 0.0f), normal));
+    else                        tangent = normalize(mk(1.0f, 0.0f, 0.0f) - normal * dot(mk(1.0f, 0.0f, 0.0f), normal));
+    bitangent = cross(normal, tangent);
+}
 
 /* ---- Halton, RTrace/sampling.metal:97-122 ------------------------------------
  * halton(i, d): f = 1; invB = 1.0f / b; while (i) { f *= invB; r += f * (i % b); i /= b; }

@@ -20,7 +20,7 @@
  *            up to 32): looked up with the per-lane primitive id after a hit,
  *            so SoA keeps different ids on different banks
  *   sshade : RT_SSHADE_ROWS rows of Sp words
- *   light  : 8 words per light      center.xyz 0 | color.xyz 0
+ *   light  : 16 words per light     center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0
  */
 #ifndef RT_SCENE_LAYOUT_H
 #define RT_SCENE_LAYOUT_H
@@ -51,14 +51,16 @@
 #define RT_SH_FLAG       15   /* 1.0f when length(emissive) > 0                      */
 #define RT_SH_METAL      16   /* mode B */
 #define RT_SH_ROUGH      17   /* mode B */
-#define RT_SHADE_ROWS    18
+#define RT_SH_TX         18   /* mode B: buildOrthonormalBasis(normal).tangent       */
+#define RT_SH_BX         21   /* mode B: buildOrthonormalBasis(normal).bitangent     */
+#define RT_SHADE_ROWS    24
 
 #define RT_SSH_DR         0
 #define RT_SSH_ER         3
 #define RT_SSH_FLAG       6
 #define RT_SSHADE_ROWS    7
 
-#define RT_LIGHT_WORDS    8
+#define RT_LIGHT_WORDS   16   /* center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0 */
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
 #define RT_CONST_SLOTS   3584
