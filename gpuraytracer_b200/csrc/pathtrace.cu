@@ -186,15 +186,22 @@ __device__ __forceinline__ bool tri_test_primary(float4 P, float4 A, float4 B, f
 
 /* sphere: m = o - c, A = d.d, B = m.d, C = m.m - r*r, disc = B*B - A*C, roots
  * (-B -+ sqrt(disc)) / A, nearer root first (rt_detmath.h: rt_sphere_test). */
-__device__ __forceinline__ bool sphere_accept(f3 m, float C, float A, f3 d, float tmin,
-                                              float bestN, float bestD, float &N_out) {
-    float B = dot(m, d);
-    float disc = fmaf(B, B, -(A * C));
-    float sq = sqrtf(fmaxf(disc, 0.0f));
-    bool real = disc >= 0.0f;
+/* stage 1: B and the discriminant.  R = center.xyz radius, or for camera rays the prepared m.xyz C */
+template <bool PRIMARY>
+__device__ __forceinline__ void sphere_disc(float4 R, f3 o, f3 d, float A, float &B, float &disc) {
+    f3 m; float C;
+    if (PRIMARY) { m = mk(R.x, R.y, R.z); C = R.w; }
+    else { m = o - mk(R.x, R.y, R.z); C = fmaf(-R.w, R.w, dot(m, m)); }
+    B = dot(m, d);
+    disc = fmaf(B, B, -(A * C));
+}
+/* stage 2, only where some lane has a real root: the square root and the two root tests */
+__device__ __forceinline__ bool sphere_roots(float B, float disc, float A, float tmin, float bestN, float bestD, float &N_out) {
+    if (!(disc >= 0.0f)) return false;
+    float sq = sqrtf(disc);
     float N0 = -B - sq, N1 = -B + sq;
-    bool ok0 = real & (N0 >= tmin * A) & (N0 * bestD < bestN * A);
-    bool ok1 = real & (N1 >= tmin * A) & (N1 * bestD < bestN * A);
+    bool ok0 = (N0 >= tmin * A) & (N0 * bestD < bestN * A);
+    bool ok1 = (N1 >= tmin * A) & (N1 * bestD < bestN * A);
     N_out = ok0 ? N0 : N1;
     return ok0 | ok1;
 }
@@ -210,8 +217,8 @@ struct SceneRef {
     __device__ __forceinline__ float4 ld(uint32_t slot) const { return CONST_BANK ? c_scene[slot] : base[slot]; }
 };
 
-/* Both loops run over the PADDED counts T4 = T rounded up to 4 and S2 = S rounded up
- * to 2 (the prepared scene pads with primitives that can never be accepted), so the
+/* Both loops run over the PADDED counts T4 = T rounded up to 4 and S4 = S rounded up
+ * to 4 (the prepared scene pads with primitives that can never be accepted), so the
  * unrolled bodies need no remainder code: less SASS, same results. */
 template <bool CONST_BANK, bool PRIMARY, int UNROLL>
 __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax,
@@ -232,21 +239,17 @@ __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o
     if (sc.S) {
         const float A = dot(d, d);
 #pragma unroll 1
-        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
+            /* four discriminants first (the common case: all negative, nothing else to do) */
+            float Bq[4], disc[4];
 #pragma unroll
-            for (uint32_t u = 0; u < 2; u++) {
-                const uint32_t j = j0 + u;
-                float N;
-                bool hit;
-                if (PRIMARY) {
-                    float4 P = sc.ld(sc.sph + 2 * j + 1);
-                    hit = sphere_accept(mk(P.x, P.y, P.z), P.w, A, d, tmin, bestN, bestD, N);
-                } else {
-                    float4 Sp = sc.ld(sc.sph + 2 * j);
-                    f3 m = o - mk(Sp.x, Sp.y, Sp.z);
-                    hit = sphere_accept(m, fmaf(-Sp.w, Sp.w, dot(m, m)), A, d, tmin, bestN, bestD, N);
+            for (uint32_t u = 0; u < 4; u++) sphere_disc<PRIMARY>(sc.ld(sc.sph + 2 * (j0 + u) + (PRIMARY ? 1 : 0)), o, d, A, Bq[u], disc[u]);
+            if (fmaxf(fmaxf(disc[0], disc[1]), fmaxf(disc[2], disc[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    if (sphere_roots(Bq[u], disc[u], A, tmin, bestN, bestD, N)) { bestN = N; bestD = A; best = sc.Treal + j0 + u; }
                 }
-                if (hit) { bestN = N; bestD = A; best = sc.Treal + j; }
             }
         }
     }
@@ -270,13 +273,16 @@ __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3
     if (sc.S) {
         const float A = dot(d, d);
 #pragma unroll 1
-        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
+            float Bq[4], disc[4];
 #pragma unroll
-            for (uint32_t u = 0; u < 2; u++) {
-                float N;
-                float4 Sp = sc.ld(sc.sph + 2 * (j0 + u));
-                f3 m = o - mk(Sp.x, Sp.y, Sp.z);
-                hit |= sphere_accept(m, fmaf(-Sp.w, Sp.w, dot(m, m)), A, d, tmin, tmax, 1.0f, N);
+            for (uint32_t u = 0; u < 4; u++) sphere_disc<false>(sc.ld(sc.sph + 2 * (j0 + u)), o, d, A, Bq[u], disc[u]);
+            if (fmaxf(fmaxf(disc[0], disc[1]), fmaxf(disc[2], disc[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    hit |= sphere_roots(Bq[u], disc[u], A, tmin, tmax, 1.0f, N);
+                }
             }
         }
     }
@@ -356,7 +362,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
 
     SceneRef<CONST_BANK> sc;
     sc.base = (const float4 *)(sm + lay.isect);
-    sc.T = (lay.T + (UNROLL - 1)) / UNROLL * UNROLL; sc.S = (lay.S + 1u) & ~1u; sc.Treal = lay.T;
+    sc.T = (lay.T + (UNROLL - 1)) / UNROLL * UNROLL; sc.S = (lay.S + 3u) & ~3u; sc.Treal = lay.T;
     sc.sph = 4 * lay.Tp;
 
     const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
