@@ -481,6 +481,19 @@ RT_PATHTRACE_ENTRY(pathTrace_exp5, false, false, 2, 8)
 RT_PATHTRACE_ENTRY(pathTrace_exp6, false, false, 4, 6)
 RT_PATHTRACE_ENTRY(pathTrace_exp7, false, false, 6, 3)
 
+#include "wave.cuh"
+#define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB)                                                              \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        pathtrace_wave_body<COUNT, UNROLL, R>(scene, offsets, out, p, lay, sm, counters);                        \
+    }
+/* warp-level path compaction, R samples per pixel per round (variant ids 8..10; rtcuda.cpp adds the queue memory) */
+RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 4, 4)
+RT_WAVE_ENTRY(pathTrace_exp9, false, 4, 8, 3)
+RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4)
+
 #include "modeb.cuh"
 
 /* ----------------------------------------------------------------- resolve ---- */

@@ -1,0 +1,231 @@
+/*
+ * wave.cuh -- `pathTrace` with warp-level path compaction (included by pathtrace.cu).
+ *
+ * Same arithmetic, same per-pixel results (bit for bit) as pathtrace_body, different
+ * scheduling.  In the per-pixel loop a lane whose path ended (miss / emissive hit) idles
+ * until the slowest path of its warp has finished its bounces: ncu shows 26.8 of 32 lanes
+ * active on average, 24.7 in the shadow loop (profiles/r01b_*).  Here a warp owns its 32
+ * pixels but traces R samples of each per ROUND (32*R paths):
+ *
+ *   1. camera rays: R passes over the 32 pixels, camera-ray form of the triangle test;
+ *      paths that land on a diffuse surface are appended to a queue in shared memory
+ *      (ballot + popc give each survivor its slot), the others deliver their radiance;
+ *   2. per bounce: the queue is consumed 32 entries at a time by FULL warps -- shade,
+ *      shadow ray, cosine continuation, closest hit -- and the survivors are appended
+ *      to the same queue in place (a chunk is read into registers before its survivors
+ *      are written, and survivors never outnumber the entries consumed);
+ *   3. every path delivers its radiance into res[sample][lane]; after the round each
+ *      lane adds its R results IN SAMPLE ORDER, so the fp32 sum is the reference's
+ *      (RTrace/raytrace.metal:103).
+ *
+ * Only the last chunk of a bounce runs with idle lanes.  No block-level barrier is
+ * involved after the scene staging: warps run independently (__syncwarp only).
+ * Queue entry (SoA, 12 words): hit point, colour (throughput), accumulated radiance,
+ * primitive id, Halton index, tag = sample*32 + lane.
+ */
+#pragma once
+
+#define RT_WAVE_FIELDS 12
+#define RT_WAVE_RES 3
+
+template <int R>
+struct WaveSmem {
+    static constexpr uint32_t CAP = 32u * R;                                  /* paths per warp per round */
+    static constexpr uint32_t WORDS_PER_WARP = (RT_WAVE_FIELDS + RT_WAVE_RES) * CAP;
+};
+
+template <bool COUNT, int UNROLL, int R>
+__device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
+                                                    float4 *__restrict__ out, const RTLaunchParams p,
+                                                    const RTSceneLayout lay, float *sm,
+                                                    unsigned long long *__restrict__ counters) {
+    constexpr uint32_t CAP = WaveSmem<R>::CAP;
+    {
+        const float4 *src = (const float4 *)scene;
+        float4 *dst = (float4 *)sm;
+        const uint32_t n4 = lay.words >> 2;
+        for (uint32_t k = threadIdx.x; k < n4; k += RT_BLOCK_THREADS) dst[k] = src[k];
+    }
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t x = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8 + (lane & 7);
+    const uint32_t ly = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4 + (lane >> 3);
+    /* out-of-image lanes stay in the warp (they help consume the queue) but own no pixel */
+    const bool owns = x < (uint32_t)p.width && ly < (uint32_t)p.rows;
+    const uint32_t y = p.tileRows ? (uint32_t)p.row0 + (ly / p.tileRows) * p.tileStride + (ly % p.tileRows)
+                                  : (uint32_t)p.row0 + ly;
+    const size_t pix = (size_t)ly * (uint32_t)p.width + x;
+
+    /* this warp's queue and result slots, after the scene */
+    float *Q = sm + lay.words + warp * WaveSmem<R>::WORDS_PER_WARP;
+    float *res = Q + RT_WAVE_FIELDS * CAP;
+    uint32_t *Qu = (uint32_t *)Q;
+#define QF(field, e) Q[(field) * CAP + (e)]
+#define QU(field, e) Qu[(field) * CAP + (e)]
+
+    SceneRef<false> sc;
+    sc.base = (const float4 *)(sm + lay.isect);
+    sc.T = (lay.T + (UNROLL - 1)) / UNROLL * UNROLL; sc.S = (lay.S + 3u) & ~3u; sc.Treal = lay.T;
+    sc.sph = 4 * lay.Tp;
+
+    const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
+    const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);
+    const f3 cam_v = mk(sm[RT_HDR_CAM_V], sm[RT_HDR_CAM_V + 1], sm[RT_HDR_CAM_V + 2]);
+    const f3 cam_w = mk(sm[RT_HDR_CAM_W], sm[RT_HDR_CAM_W + 1], sm[RT_HDR_CAM_W + 2]);
+    const float halfW = sm[RT_HDR_HALF_W], halfH = sm[RT_HDR_HALF_H];
+    const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
+    const float fx = (float)(int)x, fy = (float)(int)y;
+
+    const uint32_t offset = owns ? offsets[pix] : 0u;
+    const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
+    Counters cnt = { 0u, 0u, 0u };
+    f3 lum = mk(0.0f, 0.0f, 0.0f);
+    if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
+
+#pragma unroll 1
+    for (uint32_t k0 = 0; k0 < p.spp; k0 += R) {
+        const uint32_t nround = min((uint32_t)R, p.spp - k0);                 /* warp-uniform */
+        uint32_t count = 0;                                                   /* queue length, warp-uniform */
+
+        /* ---- 1. camera rays -------------------------------------------------------------- */
+#pragma unroll 1
+        for (uint32_t s = 0; s < nround; s++) {
+            const uint32_t i = offset + (p.firstSample + k0 + s);
+            bool alive = false;
+            uint32_t id = 0; f3 hp = mk(0.0f, 0.0f, 0.0f), r0 = hp;
+            if (owns) {
+                float jx = halton<0>(i), jy = halton<1>(i);                    /* sampling.metal:141-147 */
+                float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
+                float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
+                f3 rd = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
+                float dist;
+                if (COUNT) cnt.closest++;
+                if (closest_hit<false, true, UNROLL>(sc, cam_o, rd, 0.001f, 1000.0f, dist, id)) {
+                    const bool tri = id < lay.T;
+                    const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
+                    const uint32_t stride = tri ? lay.Tp : lay.Sp;
+                    const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
+                    if (sh[fl * stride] != 0.0f) r0 = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);
+                    else { alive = true; hp = cam_o + rd * dist; }
+                }
+            }
+            const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+            if (alive) {
+                const uint32_t e = count + __popc(mask & ((1u << lane) - 1u));
+                QF(0, e) = hp.x; QF(1, e) = hp.y; QF(2, e) = hp.z;
+                QF(3, e) = 1.0f; QF(4, e) = 1.0f; QF(5, e) = 1.0f;
+                QF(6, e) = 0.0f; QF(7, e) = 0.0f; QF(8, e) = 0.0f;
+                QU(9, e) = id; QU(10, e) = i; QU(11, e) = s * 32u + lane;
+            } else {
+                res[0 * CAP + s * 32u + lane] = r0.x; res[1 * CAP + s * 32u + lane] = r0.y; res[2 * CAP + s * 32u + lane] = r0.z;
+            }
+            count += __popc(mask);
+        }
+        __syncwarp();
+
+        /* ---- 2. bounces: consume the queue with full warps ------------------------------- */
+#pragma unroll 1
+        for (uint32_t b = 0; b < nb && count; b++) {
+            uint32_t m = 0;                                                    /* survivors written so far */
+#pragma unroll 1
+            for (uint32_t c0 = 0; c0 < count; c0 += 32) {
+                const uint32_t e = c0 + lane;
+                const bool active = e < count;
+                bool alive = false;
+                f3 hp, color, acc; uint32_t id = 0, i = 0, tag = 0;
+                if (active) {
+                    hp = mk(QF(0, e), QF(1, e), QF(2, e));
+                    color = mk(QF(3, e), QF(4, e), QF(5, e));
+                    acc = mk(QF(6, e), QF(7, e), QF(8, e));
+                    id = QU(9, e); i = QU(10, e); tag = QU(11, e);
+                }
+                __syncwarp();                                                  /* chunk is in registers: slots may be reused */
+                if (active) {
+                    f3 normal, right, fwd, diffuse;
+                    if (id < lay.T) {
+                        const float *sh = sm + lay.shade + id;
+                        normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                        right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
+                        fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
+                        diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
+                    } else {
+                        const uint32_t j = id - lay.T;
+                        const float *sh = sm + lay.sshade + j;
+                        const float *S = sm + lay.sphere + RT_SPHERE_WORDS * j;
+                        normal = normalize(hp - mk(S[0], S[1], S[2]));
+                        right = normalize(cross(normal, mk(0.0072f, 1.0f, 0.0034f)));
+                        fwd = cross(right, normal);
+                        diffuse = mk(sh[(RT_SSH_DR + 0) * lay.Sp], sh[(RT_SSH_DR + 1) * lay.Sp], sh[(RT_SSH_DR + 2) * lay.Sp]);
+                    }
+                    f3 P = hp + normal * 1e-3f;                                                 /* raytrace.metal:67 */
+                    if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
+                    float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
+                    color = color * diffuse;                                                    /* :76 */
+                    for (uint32_t l = 0; l < numLights; l++) {
+                        const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
+                        f3 ldir; float ldist;
+                        f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+                        lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
+                        if (!any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f))          /* :79-85 */
+                            acc = acc + lightColor * color;                                     /* :88 */
+                    }
+                    if (b + 1 < nb) {
+                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        f3 sdir = sample_cosine_hemisphere(ux, uy);
+                        f3 rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;              /* sampling.metal:65 */
+                        float dist;
+                        if (COUNT) cnt.closest++;
+                        if (closest_hit<false, false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id)) {     /* :49 */
+                            const bool tri = id < lay.T;
+                            const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
+                            const uint32_t stride = tri ? lay.Tp : lay.Sp;
+                            const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
+                            if (sh[fl * stride] != 0.0f) acc = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);   /* :59 */
+                            else { alive = true; hp = P + rd * dist; }
+                        }
+                    }
+                }
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+                if (alive) {
+                    const uint32_t o = m + __popc(mask & ((1u << lane) - 1u));
+                    QF(0, o) = hp.x; QF(1, o) = hp.y; QF(2, o) = hp.z;
+                    QF(3, o) = color.x; QF(4, o) = color.y; QF(5, o) = color.z;
+                    QF(6, o) = acc.x; QF(7, o) = acc.y; QF(8, o) = acc.z;
+                    QU(9, o) = id; QU(10, o) = i; QU(11, o) = tag;
+                } else if (active) {
+                    res[0 * CAP + tag] = acc.x; res[1 * CAP + tag] = acc.y; res[2 * CAP + tag] = acc.z;
+                }
+                m += __popc(mask);
+                __syncwarp();
+            }
+            count = m;
+        }
+        /* paths still queued after the last bounce cannot exist: b+1 == nb never enqueues */
+
+        /* ---- 3. in-order accumulation, raytrace.metal:103 ---------------------------------- */
+        __syncwarp();
+        for (uint32_t s = 0; s < nround; s++)
+            lum = lum + mk(res[0 * CAP + s * 32u + lane], res[1 * CAP + s * 32u + lane], res[2 * CAP + s * 32u + lane]);
+        __syncwarp();
+    }
+#undef QF
+#undef QU
+
+    if (owns) {
+        float4 o;
+        if (p.accumulate) {
+            o = make_float4(lum.x, lum.y, lum.z, (float)(p.firstSample + p.spp));
+        } else {
+            float samples = (float)p.spp;                                   /* raytrace.metal:106-109 */
+            o = make_float4(lum.x / samples, lum.y / samples, lum.z / samples, 1.0f);
+        }
+        out[pix] = o;
+    }
+    if (COUNT) {
+        atomicAdd(&counters[0], owns ? (unsigned long long)p.spp : 0ull);
+        atomicAdd(&counters[1], (unsigned long long)cnt.closest);
+        atomicAdd(&counters[2], (unsigned long long)cnt.shadow);
+        atomicAdd(&counters[3], (unsigned long long)cnt.shaded);
+    }
+}
