@@ -8,7 +8,7 @@ as hand-written CUDA for sm_100a behind a C ABI (include/rtcuda.h).
     compute_shader.py     draw_triangle: mirror of the mode-B host driver (computeShader.swift:99-189)
     distributed.py        row tiles across ranks + NCCL gather
 """
-from ._lib import (RTError, RTLaunchParams, VARIANT_CONST, VARIANT_DEFAULT, VARIANT_SMEM)  # noqa: F401
+from ._lib import (RTError, RTLaunchParams, VARIANT_CONST, VARIANT_DEFAULT, VARIANT_SMEM, VARIANT_WAVE)  # noqa: F401
 from .api import Buffer, Command, Device, Pipeline, Queue, default_params  # noqa: F401
 from .renderer import Renderer  # noqa: F401
 from .compute_shader import draw_triangle  # noqa: F401

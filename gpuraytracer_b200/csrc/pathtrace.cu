@@ -474,13 +474,6 @@ RT_PATHTRACE_ENTRY(pathTrace_smem, false, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const, true, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
-/* tuning experiments (variant ids 3..): unroll x resident blocks per SM; the winner becomes pathTrace_smem */
-RT_PATHTRACE_ENTRY(pathTrace_exp3, false, false, 4, 5)
-RT_PATHTRACE_ENTRY(pathTrace_exp4, false, false, 2, 6)
-RT_PATHTRACE_ENTRY(pathTrace_exp5, false, false, 2, 8)
-RT_PATHTRACE_ENTRY(pathTrace_exp6, false, false, 4, 6)
-RT_PATHTRACE_ENTRY(pathTrace_exp7, false, false, 6, 3)
-
 #include "wave.cuh"
 #define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB)                                                              \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
@@ -489,9 +482,13 @@ RT_PATHTRACE_ENTRY(pathTrace_exp7, false, false, 6, 3)
         extern __shared__ __align__(16) float sm[];                                                              \
         pathtrace_wave_body<COUNT, UNROLL, R>(scene, offsets, out, p, lay, sm, counters);                        \
     }
-/* warp-level path compaction, R samples per pixel per round (variant ids 8..10; rtcuda.cpp adds the queue memory) */
+/* warp-level path compaction, R samples per pixel per round; rtcuda.cpp adds the queue memory.
+ * pathTrace_wave (R = 8) is the default kernel; exp8 / exp10 (R = 4 / 2) are kept for the tuning record
+ * (profiles/r01h_variants_wave.txt), like the unroll x occupancy sweep of pathTrace_smem before them
+ * (profiles/r01c_variants.txt: all within 2 %). */
+RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3)
+RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3)
 RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 4, 4)
-RT_WAVE_ENTRY(pathTrace_exp9, false, 4, 8, 3)
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4)
 
 #include "modeb.cuh"

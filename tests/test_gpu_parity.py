@@ -77,7 +77,7 @@ def test_sincos_and_hash_bit_exact(dev):
     assert np.array_equal(got, np.array([O.lib.rt_oracle_hash(int(v)) for v in u], np.uint32))
 
 
-@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST])
+@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE])
 def test_config1_cornell_512_16spp(dev, variant):
     """BASELINE.json configs[0]: Cornell 512x512, 16 spp."""
     W = H = 512
@@ -132,7 +132,7 @@ def test_progressive_accumulation_is_bit_exact(dev):
 def test_spheres_scene_config4_small(dev):
     W, H = 192, 108
     ref, cnt = O.pathtrace(O.spheres(W, H), W, H, 4)
-    for variant in (L.VARIANT_SMEM, L.VARIANT_CONST):
+    for variant in (L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE):
         img = G.Renderer(G.init_sphere_scene(W, H), W, H, device=dev).draw(spp=4, variant=variant)
         assert out_of_tolerance(img, ref) == 0
         assert np.array_equal(img, ref)
@@ -195,6 +195,25 @@ def test_interleaved_tiles_and_exact_counters(dev):
         parts.append(np.concatenate([img, np.zeros((pad - rows, W, 4), np.float32)]))
     assert np.array_equal(np.concatenate(parts)[idx], ref)
     r = G.Renderer(sc, W, H, device=dev)
-    c = r.count_rays(spp=spp)
-    assert [c["paths"], c["closest"], c["shadow"], c["shaded"]] == [int(v) for v in cnt[:4]]
-    assert np.array_equal(r.image(), ref)
+    for variant in (L.VARIANT_SMEM, L.VARIANT_WAVE):
+        c = r.count_rays(spp=spp, variant=variant)
+        assert [c["paths"], c["closest"], c["shadow"], c["shaded"]] == [int(v) for v in cnt[:4]], variant
+        assert np.array_equal(r.image(), ref)
+
+
+def test_wave_kernel_odd_sample_counts_and_sizes(dev):
+    """The compacting kernel traces 8 samples per pixel per round: sample counts that are not multiples
+    of 8, ragged image sizes (lanes without a pixel), accumulation across launches, 1..4 bounces."""
+    W, H = 203, 77
+    sc, osc = G.init_cornell_box(W, H), O.cornell(W, H)
+    for spp, bounces in ((5, 3), (13, 2), (8, 4), (9, 1)):
+        ref, _ = O.pathtrace(osc, W, H, spp, bounces=bounces)
+        img = G.Renderer(sc, W, H, device=dev).draw(spp=spp, bounces=bounces, variant=L.VARIANT_WAVE)
+        assert np.array_equal(img, ref), (spp, bounces)
+    ref, _ = O.pathtrace(osc, W, H, 20)
+    r = G.Renderer(sc, W, H, device=dev)
+    r.clear()
+    r.draw_async(spp=7, firstSample=0, accumulate=1, variant=L.VARIANT_WAVE)
+    r.draw_async(spp=13, firstSample=7, accumulate=1, variant=L.VARIANT_WAVE).wait_until_completed()
+    acc = r.image()
+    assert np.all(acc[..., 3] == 20) and np.array_equal(acc[..., :3] / np.float32(20), ref[..., :3])

@@ -5,7 +5,7 @@ import numpy as np
 import gpuraytracer_b200 as G
 
 W, H, SPP = (int(a) for a in sys.argv[1:4]) if len(sys.argv) >= 4 else (1920, 1080, 64)
-variants = [int(v) for v in sys.argv[4].split(",")] if len(sys.argv) > 4 else [1, 2]
+variants = [int(v) for v in sys.argv[4].split(",")] if len(sys.argv) > 4 else [1, 2, 3]
 dev = G.Device(0)
 info = dev.info()
 print(info.name.decode(), info.smCount, "SMs", info.clockKHz / 1e3, "MHz")
