@@ -44,11 +44,16 @@ def parse():
     ap.add_argument("--bounces", type=int, default=3)
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--width", type=int, default=W)       # BASELINE.json configs[2]: --width 3840 --height 2160 --spp 4096
+    ap.add_argument("--height", type=int, default=H)
+    a = ap.parse_args()
+    globals()["W"], globals()["H"] = a.width, a.height
+    return a
 
 
 def workload(a):
-    return {"workload": f"Cornell box {W}x{H}, {a.spp} spp, {a.bounces} bounces (BASELINE.json configs[1])",
+    which = "configs[1]" if (W, H, a.spp) == (1920, 1080, 1024) else "configs[2]" if (W, H, a.spp) == (3840, 2160, 4096) else "custom"
+    return {"workload": f"Cornell box {W}x{H}, {a.spp} spp, {a.bounces} bounces (BASELINE.json {which})",
             "scene": "RTrace/scene.swift initCornellBox: 36 triangles, 1 light", "width": W, "height": H,
             "spp": a.spp, "bounces": a.bounces, "offsets": "hash(p + 0x9E3779B9*1) & 0xFFFFF",
             "l2": "inputs are 8.3 MB offsets + 3.6 KB scene; the kernel is compute bound (0.02 B/path), "
@@ -91,7 +96,7 @@ class ClockSampler:
 # --------------------------------------------------------------- cpu oracle ----
 def sample_rows():
     """Bounded CPU sample of the frame: 7 tiles of 8 rows spread over the image (56 rows, full width)."""
-    return [t * TILE_ROWS for t in (0, 22, 45, 67, 90, 112, 134)]
+    return [int(f * (H - TILE_ROWS)) // TILE_ROWS * TILE_ROWS for f in (0.0, 0.165, 0.336, 0.5, 0.672, 0.836, 1.0)]
 
 
 def oracle_sample(a, rows_per_tile=TILE_ROWS, tiles=None, nthreads=0):
@@ -115,7 +120,7 @@ def run_reference(a, rank):
     code of its own and its Metal shaders cannot run here) on all host cores, bounded sample per step."""
     if rank != 0:
         return
-    tiles = [536]                                   # 8 rows through the middle of the frame
+    tiles = [H // 2 // TILE_ROWS * TILE_ROWS]          # 8 rows through the middle of the frame
     for _ in range(a.warmup):
         oracle_sample(a, tiles=tiles)
     t, paths = 0.0, 0
@@ -123,7 +128,7 @@ def run_reference(a, rank):
         _, p, dt, cores = oracle_sample(a, tiles=tiles)
         t += dt; paths += p
     v = paths / t / 1e6
-    sample = f"rows 536..543 x {W} px x {a.spp} spp per step ({paths // a.steps} paths), OpenMP {cores} threads"
+    sample = f"rows {tiles[0]}..{tiles[0] + 7} x {W} px x {a.spp} spp per step ({paths // a.steps} paths), OpenMP {cores} threads"
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus,
                       "steps": a.steps, "warmup": a.warmup, "ms_per_step": t / a.steps * 1e3,
                       "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
