@@ -279,6 +279,12 @@ def run_ours(a, rank, world, local_rank):
 
 def main():
     a = parse()
+    # stdout carries exactly ONE line (the JSON): libraries that chat on fd 1 (NCCL prints its version there)
+    # are sent to stderr, and print() keeps the real stdout
+    real = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    sys.stdout = real
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
