@@ -289,6 +289,81 @@ __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3
     return hit;
 }
 
+/*
+ * Two rays from ONE origin in one pass over the primitives: the closest-hit query of the
+ * continuation ray (direction dc) and the any-hit query of the shadow ray (direction ds) of a
+ * bounce both start at the shading point (raytrace.metal:79-100).  w = v0 - o and Nn = dot(w, n)
+ * do not depend on the direction, so they -- and the three LDS.128 of the triangle record -- are
+ * shared: 36 instead of 42 FP32 instructions per triangle for the pair, and two independent
+ * dependency chains in flight.  Same operations on the same operands as tri_test, so the
+ * results are bit-identical to closest_hit + any_hit.  (Spheres: m = o - c and C are shared.)
+ */
+template <bool CONST_BANK, int UNROLL>
+__device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
+                                         f3 dc, float tminC, float tmaxC, float &dist, uint32_t &id,
+                                         f3 ds, float tminS, float tmaxS, bool &shadowed) {
+    float bestN = tmaxC, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+    bool sh = false;
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+#pragma unroll
+        for (uint32_t u = 0; u < UNROLL; u++) {
+            const uint32_t i = i0 + u;
+            const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+            const f3 v0 = mk(A.x, A.y, A.z), n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+            const f3 w = v0 - o;
+            const float Nn = dot(w, n);
+            float N, a;
+            {
+                float D = dot(dc, n);
+                f3 c = cross(w, dc);
+                float U = dot(e2, c), V = dot(e1n, c);
+                if (tri_accept(D, Nn, U, V, tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
+            }
+            {
+                float D = dot(ds, n);
+                f3 c = cross(w, ds);
+                float U = dot(e2, c), V = dot(e1n, c);
+                sh |= tri_accept(D, Nn, U, V, tminS, tmaxS, 1.0f, N, a);
+            }
+        }
+    }
+    if (sc.S) {
+        const float Ac = dot(dc, dc), As = dot(ds, ds);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
+            float Bc[4], discC[4], Bs[4], discS[4];
+#pragma unroll
+            for (uint32_t u = 0; u < 4; u++) {
+                const float4 R = sc.ld(sc.sph + 2 * (j0 + u));
+                const f3 m = o - mk(R.x, R.y, R.z);
+                const float Cq = fmaf(-R.w, R.w, dot(m, m));
+                Bc[u] = dot(m, dc); discC[u] = fmaf(Bc[u], Bc[u], -(Ac * Cq));
+                Bs[u] = dot(m, ds); discS[u] = fmaf(Bs[u], Bs[u], -(As * Cq));
+            }
+            if (fmaxf(fmaxf(discC[0], discC[1]), fmaxf(discC[2], discC[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    if (sphere_roots(Bc[u], discC[u], Ac, tminC, bestN, bestD, N)) { bestN = N; bestD = Ac; best = sc.Treal + j0 + u; }
+                }
+            }
+            if (fmaxf(fmaxf(discS[0], discS[1]), fmaxf(discS[2], discS[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    sh |= sphere_roots(Bs[u], discS[u], As, tminS, tmaxS, 1.0f, N);
+                }
+            }
+        }
+    }
+    shadowed = sh;
+    id = best;
+    dist = bestN / bestD;
+    return best != 0xffffffffu;
+}
+
 /* ---------------------------------------------------------------- shading ---- */
 /* sampling.metal:198-236 with the literals of :207-209 folded:
  * samplePosition = center + (0.25,0,0)*ux + (0,0,0.25)*uy.  The products with the

@@ -162,28 +162,36 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
                     float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
                     color = color * diffuse;                                                    /* :76 */
+                    /* the continuation ray starts at the same point as the shadow ray: it is sampled first
+                     * and traced together with the first light's shadow ray (dual_hit) */
+                    const bool cont = b + 1 < nb;                                               /* warp-uniform */
+                    f3 rd = mk(0.0f, 0.0f, 0.0f);
+                    if (cont) {
+                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        f3 sdir = sample_cosine_hemisphere(ux, uy);
+                        rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
+                        if (COUNT) cnt.closest++;
+                    }
+                    bool hitC = false; float dist = 0.0f;
                     for (uint32_t l = 0; l < numLights; l++) {
                         const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
                         f3 ldir; float ldist;
                         f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
                         lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
-                        if (!any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f))          /* :79-85 */
-                            acc = acc + lightColor * color;                                     /* :88 */
+                        bool shadowed;                                                          /* :79-85 */
+                        if (cont && l == 0)
+                            hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);   /* + :49 */
+                        else
+                            shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
+                        if (!shadowed) acc = acc + lightColor * color;                          /* :88 */
                     }
-                    if (b + 1 < nb) {
-                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
-                        f3 sdir = sample_cosine_hemisphere(ux, uy);
-                        f3 rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;              /* sampling.metal:65 */
-                        float dist;
-                        if (COUNT) cnt.closest++;
-                        if (closest_hit<false, false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id)) {     /* :49 */
-                            const bool tri = id < lay.T;
-                            const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
-                            const uint32_t stride = tri ? lay.Tp : lay.Sp;
-                            const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
-                            if (sh[fl * stride] != 0.0f) acc = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);   /* :59 */
-                            else { alive = true; hp = P + rd * dist; }
-                        }
+                    if (hitC) {
+                        const bool tri = id < lay.T;
+                        const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
+                        const uint32_t stride = tri ? lay.Tp : lay.Sp;
+                        const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
+                        if (sh[fl * stride] != 0.0f) acc = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);   /* :59 */
+                        else { alive = true; hp = P + rd * dist; }
                     }
                 }
                 const uint32_t mask = __ballot_sync(0xffffffffu, alive);

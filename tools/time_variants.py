@@ -9,7 +9,8 @@ variants = [int(v) for v in sys.argv[4].split(",")] if len(sys.argv) > 4 else [1
 dev = G.Device(0)
 info = dev.info()
 print(info.name.decode(), info.smCount, "SMs", info.clockKHz / 1e3, "MHz")
-r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+scene = G.init_sphere_scene(W, H) if os.environ.get('RT_SCENE') == 'spheres' else G.init_cornell_box(W, H)
+r = G.Renderer(scene, W, H, device=dev)
 res = {}
 ref = None
 for v in variants:
