@@ -563,8 +563,14 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
  * (profiles/r01c_variants.txt: all within 2 %). */
 RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3)
 RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3)
-RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 4, 4)
+/* R = 4: half the queue memory; the library picks it when a large scene leaves room for fewer than
+ * three R = 8 blocks per SM (256-sphere scene: 366 -> 482 Mpaths/s) */
+RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4)
+RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4)
+RT_WAVE_ENTRY(pathTrace_exp6, false, 4, 6, 4)
+RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4)
+RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2)
 
 #include "modeb.cuh"
 
