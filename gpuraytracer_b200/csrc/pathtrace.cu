@@ -150,13 +150,17 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
  */
 __device__ __forceinline__ bool tri_accept(float D, float Nn, float U, float V, float tmin,
                                            float bestN, float bestD, float &N_out, float &a_out) {
+    /* (flipping by multiplication with +-1 instead, to move work from the ALU to the FMA pipe, was measured
+     * slower: one more issue slot per test, and the kernel is bound by issue slots, not by either pipe) */
     uint32_t sgn = __float_as_uint(D) & 0x80000000u;
     U = __uint_as_float(__float_as_uint(U) ^ sgn);
     V = __uint_as_float(__float_as_uint(V) ^ sgn);
     Nn = __uint_as_float(__float_as_uint(Nn) ^ sgn);
     float a = fabsf(D);
     N_out = Nn; a_out = a;
-    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & (Nn >= tmin * a) & (Nn * bestD < bestN * a);
+    /* tmin == 0 (shadow rays; a compile-time constant after inlining): Nn >= 0, the product is skipped */
+    const bool far_enough = tmin == 0.0f ? (Nn >= 0.0f) : (Nn >= tmin * a);
+    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & far_enough & (Nn * bestD < bestN * a);
 }
 
 /* A = v0.xyz n.x | B = n.yz e2.xy | C = e2.z e1n.xyz */
@@ -362,6 +366,59 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
     id = best;
     dist = bestN / bestD;
     return best != 0xffffffffu;
+}
+
+/*
+ * Two CAMERA rays (two samples of one pixel) in one pass: the origin is the camera for both, so the
+ * four LDS.128 of a triangle record and the loop bookkeeping are shared and two independent chains
+ * are in flight.  Same operations as closest_hit<PRIMARY>: bit-identical results.
+ */
+template <bool CONST_BANK, int UNROLL>
+__device__ __forceinline__ void closest_primary2(const SceneRef<CONST_BANK> &sc, f3 d0, f3 d1, float tmin, float tmax,
+                                                 bool &hit0, float &dist0, uint32_t &id0,
+                                                 bool &hit1, float &dist1, uint32_t &id1) {
+    float bN0 = tmax, bD0 = 1.0f, bN1 = tmax, bD1 = 1.0f;
+    uint32_t b0 = 0xffffffffu, b1 = 0xffffffffu;
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+#pragma unroll
+        for (uint32_t u = 0; u < UNROLL; u++) {
+            const uint32_t i = i0 + u;
+            const float4 P = sc.ld(4 * i + 3), A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+            float N, a;
+            if (tri_test_primary(P, A, B, C, d0, tmin, bN0, bD0, N, a)) { bN0 = N; bD0 = a; b0 = i; }
+            if (tri_test_primary(P, A, B, C, d1, tmin, bN1, bD1, N, a)) { bN1 = N; bD1 = a; b1 = i; }
+        }
+    }
+    if (sc.S) {
+        const float A0 = dot(d0, d0), A1 = dot(d1, d1);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
+            float B0[4], disc0[4], B1[4], disc1[4];
+#pragma unroll
+            for (uint32_t u = 0; u < 4; u++) {
+                const float4 R = sc.ld(sc.sph + 2 * (j0 + u) + 1);
+                sphere_disc<true>(R, d0, d0, A0, B0[u], disc0[u]);
+                sphere_disc<true>(R, d1, d1, A1, B1[u], disc1[u]);
+            }
+            if (fmaxf(fmaxf(disc0[0], disc0[1]), fmaxf(disc0[2], disc0[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    if (sphere_roots(B0[u], disc0[u], A0, tmin, bN0, bD0, N)) { bN0 = N; bD0 = A0; b0 = sc.Treal + j0 + u; }
+                }
+            }
+            if (fmaxf(fmaxf(disc1[0], disc1[1]), fmaxf(disc1[2], disc1[3])) >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    float N;
+                    if (sphere_roots(B1[u], disc1[u], A1, tmin, bN1, bD1, N)) { bN1 = N; bD1 = A1; b1 = sc.Treal + j0 + u; }
+                }
+            }
+        }
+    }
+    id0 = b0; dist0 = bN0 / bD0; hit0 = b0 != 0xffffffffu;
+    id1 = b1; dist1 = bN1 / bD1; hit1 = b1 != 0xffffffffu;
 }
 
 /* ---------------------------------------------------------------- shading ---- */

@@ -7,7 +7,8 @@
  * active on average, 24.7 in the shadow loop (profiles/r01b_*).  Here a warp owns its 32
  * pixels but traces R samples of each per ROUND (32*R paths):
  *
- *   1. camera rays: R passes over the 32 pixels, camera-ray form of the triangle test;
+ *   1. camera rays: R/2 passes over the 32 pixels, two samples per pass sharing the triangle loads
+ *      (closest_primary2), camera-ray form of the triangle test;
  *      paths that land on a diffuse surface are appended to a queue in shared memory
  *      (ballot + popc give each survivor its slot), the others deliver their radiance;
  *   2. per bounce: the queue is consumed 32 entries at a time by FULL warps -- shade,
@@ -90,37 +91,56 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
 
         /* ---- 1. camera rays -------------------------------------------------------------- */
 #pragma unroll 1
-        for (uint32_t s = 0; s < nround; s++) {
-            const uint32_t i = offset + (p.firstSample + k0 + s);
-            bool alive = false;
-            uint32_t id = 0; f3 hp = mk(0.0f, 0.0f, 0.0f), r0 = hp;
+        for (uint32_t s = 0; s < nround; s += 2) {
+            /* two samples of the pixel per pass (closest_primary2); the second one is void when nround is odd */
+            const bool two = s + 1 < nround;                                   /* warp-uniform */
+            bool alive[2] = { false, false };
+            uint32_t id[2] = { 0u, 0u }, idx[2];
+            f3 hp[2], r0[2];
+            hp[0] = hp[1] = r0[0] = r0[1] = mk(0.0f, 0.0f, 0.0f);
+            idx[0] = offset + (p.firstSample + k0 + s); idx[1] = idx[0] + 1u;
             if (owns) {
-                float jx = halton<0>(i), jy = halton<1>(i);                    /* sampling.metal:141-147 */
-                float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
-                float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
-                f3 rd = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
-                float dist;
-                if (COUNT) cnt.closest++;
-                if (closest_hit<false, true, UNROLL>(sc, cam_o, rd, 0.001f, 1000.0f, dist, id)) {
-                    const bool tri = id < lay.T;
-                    const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
-                    const uint32_t stride = tri ? lay.Tp : lay.Sp;
-                    const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
-                    if (sh[fl * stride] != 0.0f) r0 = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);
-                    else { alive = true; hp = cam_o + rd * dist; }
+                f3 rd[2];
+#pragma unroll
+                for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
+                    float jx = halton<0>(idx[q]), jy = halton<1>(idx[q]);
+                    float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
+                    float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
+                    rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
+                }
+                bool hit[2]; float dist[2];
+                /* (an odd last pass traces its second ray for nothing: one code path, smaller kernel) */
+                closest_primary2<false, UNROLL>(sc, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
+                hit[1] = hit[1] && two;
+                if (COUNT) cnt.closest += two ? 2u : 1u;
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    if (hit[q]) {
+                        const bool tri = id[q] < lay.T;
+                        const float *sh = tri ? sm + lay.shade + id[q] : sm + lay.sshade + (id[q] - lay.T);
+                        const uint32_t stride = tri ? lay.Tp : lay.Sp;
+                        const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
+                        if (sh[fl * stride] != 0.0f) r0[q] = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);
+                        else { alive[q] = true; hp[q] = cam_o + rd[q] * dist[q]; }
+                    }
                 }
             }
-            const uint32_t mask = __ballot_sync(0xffffffffu, alive);
-            if (alive) {
-                const uint32_t e = count + __popc(mask & ((1u << lane) - 1u));
-                QF(0, e) = hp.x; QF(1, e) = hp.y; QF(2, e) = hp.z;
-                QF(3, e) = 1.0f; QF(4, e) = 1.0f; QF(5, e) = 1.0f;
-                QF(6, e) = 0.0f; QF(7, e) = 0.0f; QF(8, e) = 0.0f;
-                QU(9, e) = id; QU(10, e) = i; QU(11, e) = s * 32u + lane;
-            } else {
-                res[0 * CAP + s * 32u + lane] = r0.x; res[1 * CAP + s * 32u + lane] = r0.y; res[2 * CAP + s * 32u + lane] = r0.z;
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                if (q == 1 && !two) break;
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive[q]);
+                const uint32_t tag = (s + q) * 32u + lane;
+                if (alive[q]) {
+                    const uint32_t e = count + __popc(mask & ((1u << lane) - 1u));
+                    QF(0, e) = hp[q].x; QF(1, e) = hp[q].y; QF(2, e) = hp[q].z;
+                    QF(3, e) = 1.0f; QF(4, e) = 1.0f; QF(5, e) = 1.0f;
+                    QF(6, e) = 0.0f; QF(7, e) = 0.0f; QF(8, e) = 0.0f;
+                    QU(9, e) = id[q]; QU(10, e) = idx[q]; QU(11, e) = tag;
+                } else {
+                    res[0 * CAP + tag] = r0[q].x; res[1 * CAP + tag] = r0[q].y; res[2 * CAP + tag] = r0[q].z;
+                }
+                count += __popc(mask);
             }
-            count += __popc(mask);
         }
         __syncwarp();
 

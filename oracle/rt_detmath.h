@@ -192,7 +192,7 @@ RT_INLINE float rt_powf(float x, float y) {
  * which are the classic quantities scaled by the determinant: (u,v,t) =
  * (U,V,Nn)/a, never formed inside the loop.  The hit is accepted when
  *     U >= 0  &&  V >= 0  &&  U+V <= a           inside, edges inclusive, no culling
- *     Nn >= tmin*a                                 t >= tmin
+ *     Nn >= tmin*a                                 t >= tmin   (tmin == 0: Nn >= 0, no product)
  *     Nn*bestD < bestN*a                           t <  best so far (strict)
  * where (bestN,bestD) starts as (tmax,1), so the same comparison enforces
  * t < tmax, and a tie between two triangles keeps the LOWER primitive id.
@@ -230,7 +230,10 @@ RT_INLINE int rt_triangle_test(const float *v0, const float *v1, const float *v2
     float V = rt_dot3(-e1x, -e1y, -e1z, cx, cy, cz);
     if (signbit(D)) { U = -U; V = -V; Nn = -Nn; }
     float a = fabsf(D);
-    if (U >= 0.0f && V >= 0.0f && U + V <= a && Nn >= tmin * a && Nn * *bestD < *bestN * a) {
+    /* t >= tmin: for tmin == 0 (shadow rays) the comparison is Nn >= 0 and the product 0*a is not formed
+     * (it would differ only for an infinite a) */
+    int farEnough = tmin == 0.0f ? (Nn >= 0.0f) : (Nn >= tmin * a);
+    if (U >= 0.0f && V >= 0.0f && U + V <= a && farEnough && Nn * *bestD < *bestN * a) {
         *bestN = Nn; *bestD = a;
         return 1;
     }
