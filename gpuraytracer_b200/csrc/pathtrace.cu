@@ -369,6 +369,70 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
 }
 
 /*
+ * N shadow rays from ONE origin (scenes with several lights: one shadow ray per light per bounce, all
+ * from the shading point): w, Nn (triangles) and m, C (spheres) are computed once per primitive.
+ */
+template <bool CONST_BANK, int UNROLL, int N>
+__device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3 o, const f3 (&d)[N], const float (&tmax)[N],
+                                              bool (&shadowed)[N]) {
+    bool sh[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) sh[r] = false;
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+#pragma unroll
+        for (uint32_t u = 0; u < UNROLL; u++) {
+            const uint32_t i = i0 + u;
+            const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+            const f3 v0 = mk(A.x, A.y, A.z), n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+            const f3 w = v0 - o;
+            const float Nn = dot(w, n);
+#pragma unroll
+            for (int r = 0; r < N; r++) {
+                float Nq, a;
+                float D = dot(d[r], n);
+                f3 c = cross(w, d[r]);
+                float U = dot(e2, c), V = dot(e1n, c);
+                sh[r] |= tri_accept(D, Nn, U, V, 0.0f, tmax[r], 1.0f, Nq, a);
+            }
+        }
+    }
+    if (sc.S) {
+        float Aq[N];
+#pragma unroll
+        for (int r = 0; r < N; r++) Aq[r] = dot(d[r], d[r]);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+            float Bq[2][N], disc[2][N];
+            float mx = -1.0f;
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                const float4 R = sc.ld(sc.sph + 2 * (j0 + u));
+                const f3 m = o - mk(R.x, R.y, R.z);
+                const float Cq = fmaf(-R.w, R.w, dot(m, m));
+#pragma unroll
+                for (int r = 0; r < N; r++) {
+                    Bq[u][r] = dot(m, d[r]);
+                    disc[u][r] = fmaf(Bq[u][r], Bq[u][r], -(Aq[r] * Cq));
+                    mx = fmaxf(mx, disc[u][r]);
+                }
+            }
+            if (mx >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 2; u++)
+#pragma unroll
+                    for (int r = 0; r < N; r++) {
+                        float Nq;
+                        sh[r] |= sphere_roots(Bq[u][r], disc[u][r], Aq[r], 0.0f, tmax[r], 1.0f, Nq);
+                    }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < N; r++) shadowed[r] = sh[r];
+}
+
+/*
  * Two CAMERA rays (two samples of one pixel) in one pass: the origin is the camera for both, so the
  * four LDS.128 of a triangle record and the loop bookkeeping are shared and two independent chains
  * are in flight.  Same operations as closest_hit<PRIMARY>: bit-identical results.

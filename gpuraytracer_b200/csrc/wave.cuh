@@ -193,17 +193,51 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                         if (COUNT) cnt.closest++;
                     }
                     bool hitC = false; float dist = 0.0f;
-                    for (uint32_t l = 0; l < numLights; l++) {
-                        const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
+                    /* shadow rays, one per light (:79-88; the reference has one light).  The first one rides with
+                     * the continuation ray (dual_hit), the others go three / two at a time (any_hit_multi): every
+                     * ray of a bounce starts at P, so the origin-dependent part of each test is shared. */
+                    if (numLights == 1) {            /* the reference's case: its own straight-line code */
+                        const float *L = sm + lay.light;
                         f3 ldir; float ldist;
                         f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
                         lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
-                        bool shadowed;                                                          /* :79-85 */
-                        if (cont && l == 0)
-                            hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);   /* + :49 */
-                        else
-                            shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
+                        bool shadowed;
+                        if (cont) hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
+                        else shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
                         if (!shadowed) acc = acc + lightColor * color;                          /* :88 */
+                    } else {
+                        uint32_t l = 0;
+                        while (l < numLights) {
+                            const uint32_t left = numLights - l;
+                            const uint32_t n = (cont && l == 0) ? 1u : (left >= 3u ? 3u : left);
+                            f3 ldir[3], lcol[3]; float ltmax[3]; bool shd[3] = { false, false, false };
+#pragma unroll
+                            for (uint32_t r = 0; r < 3; r++) {
+                                ldir[r] = mk(0.0f, 1.0f, 0.0f); lcol[r] = mk(0.0f, 0.0f, 0.0f); ltmax[r] = 0.0f;
+                                if (r < n) {
+                                    const float *L = sm + lay.light + RT_LIGHT_WORDS * (l + r);
+                                    float ldist;
+                                    lcol[r] = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir[r], ldist);
+                                    lcol[r] = lcol[r] * saturate(dot(normal, ldir[r]));             /* :75 */
+                                    ltmax[r] = ldist - 1e-3f;
+                                }
+                            }
+                            if (cont && l == 0) {
+                                hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);   /* + :49 */
+                            } else if (n == 3) {
+                                any_hit_multi<false, 2, 3>(sc, P, ldir, ltmax, shd);
+                            } else if (n == 2) {
+                                f3 d2[2] = { ldir[0], ldir[1] }; float t2[2] = { ltmax[0], ltmax[1] }; bool s2[2];
+                                any_hit_multi<false, 2, 2>(sc, P, d2, t2, s2);
+                                shd[0] = s2[0]; shd[1] = s2[1];
+                            } else {
+                                shd[0] = any_hit<false, UNROLL>(sc, P, ldir[0], 0.0f, ltmax[0]);
+                            }
+#pragma unroll
+                            for (uint32_t r = 0; r < 3; r++)
+                                if (r < n && !shd[r]) acc = acc + lcol[r] * color;                  /* :88, in light order */
+                            l += n;
+                        }
                     }
                     if (hitC) {
                         const bool tri = id < lay.T;
