@@ -217,3 +217,25 @@ def test_wave_kernel_odd_sample_counts_and_sizes(dev):
     r.draw_async(spp=13, firstSample=7, accumulate=1, variant=L.VARIANT_WAVE).wait_until_completed()
     acc = r.image()
     assert np.all(acc[..., 3] == 20) and np.array_equal(acc[..., :3] / np.float32(20), ref[..., :3])
+
+
+def test_group_render_single_process_row_tiles(dev):
+    """rtGroupRender: one process, one host thread per device, contiguous row tiles, host gather.
+    Two group members on the same GPU exercise the split without needing a second device."""
+    W, H, spp = 160, 90, 6
+    osc = O.cornell(W, H)
+    ref, _ = O.pathtrace(osc, W, H, spp)
+    off = O.offsets(W, 0, H)
+    for ordinals in ([0], [0, 0], [0, 0, 0]):
+        arr = (C.c_int * len(ordinals))(*ordinals)
+        g = C.c_void_p()
+        L.check(L.lib.rtGroupCreate(arr, len(ordinals), C.byref(g)), "rtGroupCreate")
+        assert L.lib.rtGroupDeviceCount(g) == len(ordinals)
+        p = G.default_params(W, H, spp=spp, numTriangles=36, numLights=1)
+        out = np.zeros((H, W, 4), np.float32)
+        ms = C.c_double()
+        L.check(L.lib.rtGroupRender(g, b"pathTrace", O.vp(osc["camera"]), O.vp(osc["materials"]), osc["materials"].nbytes,
+                                    O.vp(osc["lights"]), osc["lights"].nbytes, O.vp(osc["vertices"]), osc["vertices"].nbytes,
+                                    None, 0, O.vp(off), C.byref(p), O.vp(out), C.byref(ms)), "rtGroupRender")
+        L.check(L.lib.rtGroupRelease(g), "rtGroupRelease")
+        assert ms.value > 0 and np.array_equal(out, ref), ordinals
