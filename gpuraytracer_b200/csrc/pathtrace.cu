@@ -485,6 +485,131 @@ __device__ __forceinline__ void closest_primary2(const SceneRef<CONST_BANK> &sc,
     id1 = b1; dist1 = bN1 / bD1; hit1 = b1 != 0xffffffffu;
 }
 
+/*
+ * closest_primary2 over a CANDIDATE LIST: bit k of cullT[wd] / cullS[wd] says primitive 32*wd + k may be
+ * hit by a camera ray through this warp's pixels (camera_candidates below; warp-uniform words in shared
+ * memory).  Candidates are visited in ascending index, like the full loop, so the strict-less tie rule
+ * picks the same primitive; a primitive that is left out could not have been accepted.  Two candidates per
+ * pass; an odd one is paired with itself (a second test of the same primitive never passes the
+ * strict-less comparison against its own distance).
+ */
+__device__ __forceinline__ void closest_primary2_list(const SceneRef<false> &sc, const uint32_t *cullT, uint32_t mwT,
+                                                      const uint32_t *cullS, uint32_t mwS,
+                                                      f3 d0, f3 d1, float tmin, float tmax,
+                                                      bool &hit0, float &dist0, uint32_t &id0,
+                                                      bool &hit1, float &dist1, uint32_t &id1) {
+    float bN0 = tmax, bD0 = 1.0f, bN1 = tmax, bD1 = 1.0f;
+    uint32_t b0 = 0xffffffffu, b1 = 0xffffffffu;
+#pragma unroll 1
+    for (uint32_t wd = 0; wd < mwT; wd++) {
+        uint32_t m = cullT[wd];
+#pragma unroll 1
+        while (m) {
+            const uint32_t i = (wd << 5) + (uint32_t)__ffs((int)m) - 1u; m &= m - 1u;
+            uint32_t j = i;
+            if (m) { j = (wd << 5) + (uint32_t)__ffs((int)m) - 1u; m &= m - 1u; }
+            const float4 Pi = sc.ld(4 * i + 3), Ai = sc.ld(4 * i), Bi = sc.ld(4 * i + 1), Ci = sc.ld(4 * i + 2);
+            const float4 Pj = sc.ld(4 * j + 3), Aj = sc.ld(4 * j), Bj = sc.ld(4 * j + 1), Cj = sc.ld(4 * j + 2);
+            float N, a;
+            if (tri_test_primary(Pi, Ai, Bi, Ci, d0, tmin, bN0, bD0, N, a)) { bN0 = N; bD0 = a; b0 = i; }
+            if (tri_test_primary(Pi, Ai, Bi, Ci, d1, tmin, bN1, bD1, N, a)) { bN1 = N; bD1 = a; b1 = i; }
+            if (tri_test_primary(Pj, Aj, Bj, Cj, d0, tmin, bN0, bD0, N, a)) { bN0 = N; bD0 = a; b0 = j; }
+            if (tri_test_primary(Pj, Aj, Bj, Cj, d1, tmin, bN1, bD1, N, a)) { bN1 = N; bD1 = a; b1 = j; }
+        }
+    }
+    if (mwS) {
+        const float A0 = dot(d0, d0), A1 = dot(d1, d1);
+#pragma unroll 1
+        for (uint32_t wd = 0; wd < mwS; wd++) {
+            uint32_t m = cullS[wd];
+#pragma unroll 1
+            while (m) {
+                const uint32_t i = (wd << 5) + (uint32_t)__ffs((int)m) - 1u; m &= m - 1u;
+                uint32_t j = i;
+                if (m) { j = (wd << 5) + (uint32_t)__ffs((int)m) - 1u; m &= m - 1u; }
+                const float4 Ri = sc.ld(sc.sph + 2 * i + 1), Rj = sc.ld(sc.sph + 2 * j + 1);
+                float B, disc, N;
+                sphere_disc<true>(Ri, d0, d0, A0, B, disc);
+                if (sphere_roots(B, disc, A0, tmin, bN0, bD0, N)) { bN0 = N; bD0 = A0; b0 = sc.Treal + i; }
+                sphere_disc<true>(Ri, d1, d1, A1, B, disc);
+                if (sphere_roots(B, disc, A1, tmin, bN1, bD1, N)) { bN1 = N; bD1 = A1; b1 = sc.Treal + i; }
+                sphere_disc<true>(Rj, d0, d0, A0, B, disc);
+                if (sphere_roots(B, disc, A0, tmin, bN0, bD0, N)) { bN0 = N; bD0 = A0; b0 = sc.Treal + j; }
+                sphere_disc<true>(Rj, d1, d1, A1, B, disc);
+                if (sphere_roots(B, disc, A1, tmin, bN1, bD1, N)) { bN1 = N; bD1 = A1; b1 = sc.Treal + j; }
+            }
+        }
+    }
+    id0 = b0; dist0 = bN0 / bD0; hit0 = b0 != 0xffffffffu;
+    id1 = b1; dist1 = bN1 / bD1; hit1 = b1 != 0xffffffffu;
+}
+
+/*
+ * Camera-ray candidates of one warp.  Every camera ray of the warp passes through the pixel rectangle
+ * [x0, x1+1) x [y0, y1+1) of the image plane (sampling.metal:141-147: pixel + jitter in [0,1)), so a
+ * primitive whose perspective projection stays clear of that rectangle by more than one pixel cannot be
+ * hit: lane l projects primitive 32*wd + l (its three vertices; for a sphere the box bound of x/z and
+ * y/z over its bounding cube), and the ballot of "not provably outside" is the candidate word.
+ * The exact test's own rounding lets it accept rays a few 1e-4 pixel outside the true silhouette
+ * (error of U, V ~ 1e-5 against a = |d.n| ~ |n| cos(theta)); the one-pixel margin covers that unless
+ * the primitive is seen within 0.6 degrees of edge-on (or reaches behind the camera, or is a speck),
+ * and those are always kept.  Every comparison is written so that a NaN keeps the primitive.
+ */
+struct CameraFrame { f3 o, u, v, w; float halfW, halfH, resX, resY; };
+
+__device__ __forceinline__ void project_px(const CameraFrame &cf, f3 q, float &X, float &Y, float &zc) {
+    zc = -dot(q, cf.w);
+    const float xc = dot(q, cf.u), yc = dot(q, cf.v);
+    X = (xc / (zc * cf.halfW) + 1.0f) * (0.5f * cf.resX);
+    Y = (1.0f - yc / (zc * cf.halfH)) * (0.5f * cf.resY);
+}
+
+__device__ __forceinline__ void camera_candidates(const SceneRef<false> &sc, const CameraFrame &cf, uint32_t nT, uint32_t nS,
+                                                  float rx0, float rx1, float ry0, float ry1,
+                                                  uint32_t *cullT, uint32_t mwT, uint32_t *cullS, uint32_t mwS, uint32_t lane) {
+    for (uint32_t wd = 0; wd < mwT; wd++) {
+        const uint32_t i = (wd << 5) + lane;
+        bool keep = false;
+        if (i < nT) {
+            const float4 P = sc.ld(4 * i + 3), A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+            const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+            const f3 q0 = mk(P.x, P.y, P.z), q1 = q0 - e1n, q2 = q0 + e2;
+            float X0, Y0, z0, X1, Y1, z1, X2, Y2, z2;
+            project_px(cf, q0, X0, Y0, z0); project_px(cf, q1, X1, Y1, z1); project_px(cf, q2, X2, Y2, z2);
+            const float far2 = fmaxf(fmaxf(dot(q0, q0), dot(q1, q1)), dot(q2, q2));
+            const float far = sqrtf(far2);
+            const bool safe = (fminf(fminf(z0, z1), z2) > 0.01f * far) && (fabsf(P.w) > 0.01f * far * sqrtf(dot(n, n)));
+            const bool outside = (fmaxf(fmaxf(X0, X1), X2) < rx0) || (fminf(fminf(X0, X1), X2) > rx1) ||
+                                 (fmaxf(fmaxf(Y0, Y1), Y2) < ry0) || (fminf(fminf(Y0, Y1), Y2) > ry1);
+            keep = !(safe && outside);
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) cullT[wd] = word;
+    }
+    for (uint32_t wd = 0; wd < mwS; wd++) {
+        const uint32_t j = (wd << 5) + lane;
+        bool keep = false;
+        if (j < nS) {
+            const float4 Sg = sc.ld(sc.sph + 2 * j);
+            const f3 q = mk(Sg.x, Sg.y, Sg.z) - cf.o;
+            const float r = fabsf(Sg.w);
+            const float zc = -dot(q, cf.w), xc = dot(q, cf.u), yc = dot(q, cf.v);
+            const float far = sqrtf(dot(q, q));
+            const bool safe = (zc - r > 0.01f * (far + r)) && (r > 1e-3f * far);
+            const float zn = zc - r, zf = zc + r;
+            const float txh = (xc + r) / ((xc + r >= 0.0f) ? zn : zf), txl = (xc - r) / ((xc - r <= 0.0f) ? zn : zf);
+            const float tyh = (yc + r) / ((yc + r >= 0.0f) ? zn : zf), tyl = (yc - r) / ((yc - r <= 0.0f) ? zn : zf);
+            const float Xh = (txh / cf.halfW + 1.0f) * (0.5f * cf.resX), Xl = (txl / cf.halfW + 1.0f) * (0.5f * cf.resX);
+            const float Yl = (1.0f - tyh / cf.halfH) * (0.5f * cf.resY), Yh = (1.0f - tyl / cf.halfH) * (0.5f * cf.resY);
+            const bool outside = (Xh < rx0) || (Xl > rx1) || (Yh < ry0) || (Yl > ry1);
+            keep = !(safe && outside);
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) cullS[wd] = word;
+    }
+    __syncwarp();
+}
+
 /* ---------------------------------------------------------------- shading ---- */
 /* sampling.metal:198-236 with the literals of :207-209 folded:
  * samplePosition = center + (0.25,0,0)*ux + (0,0,0.25)*uy.  The products with the

@@ -78,6 +78,19 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const float fx = (float)(int)x, fy = (float)(int)y;
 
+    /* ---- 0. which primitives can a camera ray of this warp's pixels hit?  (camera_candidates) ---- */
+    const uint32_t mwT = (lay.T + 31u) >> 5, mwS = (lay.S + 31u) >> 5;
+    uint32_t *cullT = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * WaveSmem<R>::WORDS_PER_WARP) + warp * (mwT + mwS);
+    uint32_t *cullS = cullT + mwT;
+    {
+        CameraFrame cf = { cam_o, cam_u, cam_v, cam_w, halfW, halfH, resX, resY };
+        const int big = 0x3fffffff;
+        const int x0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), x1 = __reduce_max_sync(0xffffffffu, owns ? (int)x : -big);
+        const int y0 = __reduce_min_sync(0xffffffffu, owns ? (int)y : big), y1 = __reduce_max_sync(0xffffffffu, owns ? (int)y : -big);
+        camera_candidates(sc, cf, lay.T, lay.S, (float)x0 - 1.0f, (float)x1 + 2.0f, (float)y0 - 1.0f, (float)y1 + 2.0f,
+                          cullT, mwT, cullS, mwS, lane);
+    }
+
     const uint32_t offset = owns ? offsets[pix] : 0u;
     const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
     Counters cnt = { 0u, 0u, 0u };
@@ -110,7 +123,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                 }
                 bool hit[2]; float dist[2];
                 /* (an odd last pass traces its second ray for nothing: one code path, smaller kernel) */
-                closest_primary2<false, UNROLL>(sc, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
+                closest_primary2_list(sc, cullT, mwT, cullS, mwS, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
                 hit[1] = hit[1] && two;
                 if (COUNT) cnt.closest += two ? 2u : 1u;
 #pragma unroll
