@@ -239,3 +239,37 @@ def test_group_render_single_process_row_tiles(dev):
                                     None, 0, O.vp(off), C.byref(p), O.vp(out), C.byref(ms)), "rtGroupRender")
         L.check(L.lib.rtGroupRelease(g), "rtGroupRelease")
         assert ms.value > 0 and np.array_equal(out, ref), ordinals
+
+
+def _set_camera(cam_bytes, pos, direction, up=(0.0, 1.0, 0.0), fov=None):
+    f = cam_bytes.view(np.float32)               # CameraGPU: position@0, direction@16, up@32, fov@56 (shaderTypes.h)
+    f[0:3] = pos; f[4:7] = direction; f[8:11] = up
+    if fov is not None:
+        f[14] = fov
+
+
+@pytest.mark.parametrize("scene_name", ["cornell", "spheres"])
+def test_camera_candidate_lists_moved_cameras(dev, scene_name):
+    """The wave kernel tests camera rays only against the primitives whose projection touches the warp's
+    pixels (camera_candidates).  Cameras that put primitives behind the eye, edge-on (eye in a wall's plane),
+    across the whole screen (eye inside the sphere lattice), rolled and wide-angle must still give the
+    oracle's image bit for bit."""
+    W, H, spp = 96, 64, 4
+    cams = [((0.0, 0.0, 9.0), (0.0, 0.0, -1.0), (0.0, 1.0, 0.0), None),          # the fixture's own
+            ((0.3, -0.4, 1.0), (0.2, -0.1, -1.0), (0.0, 1.0, 0.0), 1.6),           # inside the room, walls behind the eye
+            ((2.5, 0.0, 2.0), (-0.3, 0.0, -1.0), (0.0, 1.0, 0.0), 1.2),            # eye in the plane of the right wall
+            ((0.0, -2.5, 6.0), (0.0, 0.02, -1.0), (0.0, 1.0, 0.0), None),          # eye in the floor plane
+            ((-1.2, 1.9, 0.4), (0.5, -0.8, -0.3), (0.3, 1.0, 0.1), 2.4),           # looking down, rolled, very wide
+            ((0.0, 0.0, -1.0), (0.0, 0.3, 1.0), (0.0, 1.0, 0.0), 1.0)]             # looking out of the open front
+    for pos, direction, up, fov in cams:
+        osc = O.cornell(W, H) if scene_name == "cornell" else O.spheres(W, H)
+        gsc = G.init_cornell_box(W, H) if scene_name == "cornell" else G.init_sphere_scene(W, H)
+        _set_camera(osc["camera"], pos, direction, up, fov)
+        _set_camera(gsc.camera, pos, direction, up, fov)
+        assert np.array_equal(osc["camera"], gsc.camera)
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        r = G.Renderer(gsc, W, H, device=dev)
+        img = r.draw(spp=spp, variant=L.VARIANT_WAVE)
+        full = r.draw(spp=spp, variant=L.VARIANT_SMEM)                    # the kernel without candidate lists
+        assert np.array_equal(full, ref), (pos, "smem")
+        assert np.array_equal(img, ref), (pos, "wave", int((img != ref).sum()))
