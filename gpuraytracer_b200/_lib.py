@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtcuda.so")
+LIB_PATH = os.environ.get("RTCUDA_LIB") or os.path.join(_HERE, "librtcuda.so")   # (override: kernel A/B experiments)
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

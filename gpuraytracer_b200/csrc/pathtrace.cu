@@ -77,12 +77,12 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             f3 v1 = mk(vv[1].x, vv[1].y, vv[1].z);
             f3 v2 = mk(vv[2].x, vv[2].y, vv[2].z);
             f3 e1 = v1 - v0, e2 = v2 - v0;
-            f3 nn = cross(e1, e2);                 /* un-normalised: the intersector's n */
+            f3 nn = cross(e1, e2);                 /* un-normalised; the intersector's n is -nn (tri_accept) */
             f3 w = v0 - position;                  /* camera rays: w and Nn do not depend on the ray */
-            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = nn.x;
-            is[4] = nn.y; is[5] = nn.z; is[6] = e2.x; is[7] = e2.y;
+            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = -nn.x;
+            is[4] = -nn.y; is[5] = -nn.z; is[6] = e2.x; is[7] = e2.y;
             is[8] = e2.z; is[9] = -e1.x; is[10] = -e1.y; is[11] = -e1.z;
-            ps[0] = w.x; ps[1] = w.y; ps[2] = w.z; ps[3] = dot(w, nn);
+            ps[0] = w.x; ps[1] = w.y; ps[2] = w.z; ps[3] = dot(w, -nn);
             f3 n = normalize(nn);                                            /* sampling.metal:16-26 */
             f3 right = normalize(cross(n, mk(0.0072f, 1.0f, 0.0034f)));      /* sampling.metal:57   */
             f3 fwd = cross(right, n);                                        /* sampling.metal:61   */
@@ -140,27 +140,30 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
 /*
  * Division-free ray/triangle test in the form fixed by the arithmetic contract
  * (oracle/rt_detmath.h states the same thing for the CPU): with the
- * per-triangle constants n = cross(e1,e2), e2, e1n = -e1 and, per ray,
- *     w = v0 - o, D = dot(d,n), Nn = dot(w,n), c = cross(w,d), U = dot(e2,c), V = dot(e1n,c),
- * everything multiplied by sign(D) and a = |D|, a hit needs
- *     U >= 0, V >= 0, U + V <= a, Nn >= tmin*a, Nn*bestD < bestN*a.
+ * per-triangle constants n = -cross(e1,e2), e2, e1n = -e1 and, per ray,
+ *     w = v0 - o, D = dot(d,n), Nn = dot(w,n), c = -cross(w,d), U = dot(e2,c), V = dot(e1n,c),
+ * and a = |D|, a hit needs U, V and Nn to carry the sign bit of D and
+ *     |U + V| <= a, |Nn| >= tmin*a, |Nn|*bestD < bestN*a.
  * (bestN,bestD) starts at (tmax,1).  One division, bestN/bestD, after the loop.
  * 21 FP32 instructions + the comparisons; for camera rays w and Nn come from the
  * prepared scene (they depend on the camera position only), leaving 15.
  */
 __device__ __forceinline__ bool tri_accept(float D, float Nn, float U, float V, float tmin,
                                            float bestN, float bestD, float &N_out, float &a_out) {
-    /* (flipping by multiplication with +-1 instead, to move work from the ALU to the FMA pipe, was measured
-     * slower: one more issue slot per test, and the kernel is bound by issue slots, not by either pipe) */
-    uint32_t sgn = __float_as_uint(D) & 0x80000000u;
-    U = __uint_as_float(__float_as_uint(U) ^ sgn);
-    V = __uint_as_float(__float_as_uint(V) ^ sgn);
-    Nn = __uint_as_float(__float_as_uint(Nn) ^ sgn);
-    float a = fabsf(D);
-    N_out = Nn; a_out = a;
-    /* tmin == 0 (shadow rays; a compile-time constant after inlining): Nn >= 0, the product is skipped */
-    const bool far_enough = tmin == 0.0f ? (Nn >= 0.0f) : (Nn >= tmin * a);
-    return (U >= 0.0f) & (V >= 0.0f) & (U + V <= a) & far_enough & (Nn * bestD < bestN * a);
+    /* sign rule: U, V and Nn must carry D's sign bit -- two LOP3 and one ISETP for all three.
+     * (History, all measured on B200 with the results unchanged: flipping each quantity by XOR and comparing
+     * it with 0 costs three more issue slots per test, 4 % of the frame; flipping by integer add, or by
+     * multiplication with +-1 to move work to the FMA pipe, was slower still: the loop is bound by issue
+     * slots, and a half-rate ALU instruction costs 1.2-1.5 of them, tools/gen_issue_bench.py.) */
+    const uint32_t db = __float_as_uint(D);
+    const uint32_t t1 = (__float_as_uint(U) ^ db) | (__float_as_uint(V) ^ db);
+    const int t2 = (int)(t1 | (__float_as_uint(Nn) ^ db));
+    const float s = U + V;
+    const float a = fabsf(D), N = fabsf(Nn);
+    N_out = N; a_out = a;
+    /* tmin == 0 (shadow rays; a compile-time constant after inlining): the sign rule is the whole test */
+    if (tmin == 0.0f) return (t2 >= 0) & (fabsf(s) <= a) & (N * bestD < bestN * a);
+    return (t2 >= 0) & (fabsf(s) <= a) & (N >= tmin * a) & (N * bestD < bestN * a);
 }
 
 /* A = v0.xyz n.x | B = n.yz e2.xy | C = e2.z e1n.xyz */
@@ -170,7 +173,7 @@ __device__ __forceinline__ bool tri_test(float4 A, float4 B, float4 C, f3 o, f3 
     f3 w = v0 - o;
     float D = dot(d, n);
     float Nn = dot(w, n);
-    f3 c = cross(w, d);
+    f3 c = -cross(w, d);
     float U = dot(e2, c);
     float V = dot(e1n, c);
     return tri_accept(D, Nn, U, V, tmin, bestN, bestD, N_out, a_out);
@@ -182,7 +185,7 @@ __device__ __forceinline__ bool tri_test_primary(float4 P, float4 A, float4 B, f
     f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
     f3 w = mk(P.x, P.y, P.z);
     float D = dot(d, n);
-    f3 c = cross(w, d);
+    f3 c = -cross(w, d);
     float U = dot(e2, c);
     float V = dot(e1n, c);
     return tri_accept(D, P.w, U, V, tmin, bestN, bestD, N_out, a_out);
@@ -321,13 +324,13 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
             float N, a;
             {
                 float D = dot(dc, n);
-                f3 c = cross(w, dc);
+                f3 c = -cross(w, dc);
                 float U = dot(e2, c), V = dot(e1n, c);
                 if (tri_accept(D, Nn, U, V, tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
             }
             {
                 float D = dot(ds, n);
-                f3 c = cross(w, ds);
+                f3 c = -cross(w, ds);
                 float U = dot(e2, c), V = dot(e1n, c);
                 sh |= tri_accept(D, Nn, U, V, tminS, tmaxS, 1.0f, N, a);
             }
@@ -391,7 +394,7 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
             for (int r = 0; r < N; r++) {
                 float Nq, a;
                 float D = dot(d[r], n);
-                f3 c = cross(w, d[r]);
+                f3 c = -cross(w, d[r]);
                 float U = dot(e2, c), V = dot(e1n, c);
                 sh[r] |= tri_accept(D, Nn, U, V, 0.0f, tmax[r], 1.0f, Nq, a);
             }

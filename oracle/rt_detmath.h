@@ -185,18 +185,26 @@ RT_INLINE float rt_powf(float x, float y) {
  *
  * and per ray (o,d):
  *
- *     w  = v0 - o              D  = dot(d, n)         Nn = dot(w, n)
- *     c  = cross(w, d)         U  = dot(e2, c)        V  = dot(e1n, c)
- *     if D < 0 (sign bit set): U,V,Nn = -U,-V,-Nn ;   a = |D|
+ *     w  = v0 - o              D  = dot(d, n)         Nn = dot(w, n)         (n  = -(e1 x e2))
+ *     c  = -cross(w, d)        U  = dot(e2, c)        V  = dot(e1n, c)
+ *     a = |D|
  *
  * which are the classic quantities scaled by the determinant: (u,v,t) =
- * (U,V,Nn)/a, never formed inside the loop.  The hit is accepted when
- *     U >= 0  &&  V >= 0  &&  U+V <= a           inside, edges inclusive, no culling
- *     Nn >= tmin*a                                 t >= tmin   (tmin == 0: Nn >= 0, no product)
- *     Nn*bestD < bestN*a                           t <  best so far (strict)
+ * (U,V,Nn)/D, never formed inside the loop.  The hit is accepted when
+ *     signbit(U) == signbit(V) == signbit(Nn) == signbit(D)     u >= 0, v >= 0, t >= 0, no culling
+ *     |U+V| <= a                                   u + v <= 1, edge inclusive
+ *     |Nn| >= tmin*a                               t >= tmin   (tmin == 0: the sign rule alone, no product)
+ *     |Nn|*bestD < bestN*a                         t <  best so far (strict)
  * where (bestN,bestD) starts as (tmax,1), so the same comparison enforces
  * t < tmax, and a tie between two triangles keeps the LOWER primitive id.
- * D == 0 can never pass (it would need Nn >= 0 and Nn < 0).  The reported
+ * (The sign rule is the integer form of "U, V, Nn flipped by sign(D) are >= 0": on the GPU it is two
+ * three-input logic operations and one integer compare for all three quantities, where flipping and
+ * comparing each one costs three more issue slots per test.  The two forms differ only for an exact
+ * zero whose sign bit is not D's.  An exact zero of U or V -- a ray through an edge -- comes out of a
+ * cancellation as +0, and with n and c negated as above D is POSITIVE where the ray meets the side the
+ * winding normal e1 x e2 points to: there both triangles of a shared edge accept and the lower id wins,
+ * as with the inclusive comparison; on a back face such a ray is accepted by neither.)
+ * D == 0 can never pass (|Nn|*bestD < bestN*0 is false).  The reported
  * distance is the single division bestN/bestD after the loop.
  * Cost: 21 multiply/add instructions per test (w 3, D 3, Nn 3, c 6, U 3, V 3),
  * 32 flop, + 4 flop for the comparisons' products and sum.
@@ -222,19 +230,22 @@ RT_INLINE int rt_triangle_test(const float *v0, const float *v1, const float *v2
     float e2x = v2[0] - v0[0], e2y = v2[1] - v0[1], e2z = v2[2] - v0[2];
     float nx, ny, nz, cx, cy, cz;
     rt_cross3(e1x, e1y, e1z, e2x, e2y, e2z, &nx, &ny, &nz);
+    nx = -nx; ny = -ny; nz = -nz;                           /* n = -(e1 x e2) */
     float wx = v0[0] - o[0], wy = v0[1] - o[1], wz = v0[2] - o[2];
     float D  = rt_dot3(d[0], d[1], d[2], nx, ny, nz);
     float Nn = rt_dot3(wx, wy, wz, nx, ny, nz);
     rt_cross3(wx, wy, wz, d[0], d[1], d[2], &cx, &cy, &cz);
+    cx = -cx; cy = -cy; cz = -cz;                           /* c = -(w x d) */
     float U = rt_dot3(e2x, e2y, e2z, cx, cy, cz);
     float V = rt_dot3(-e1x, -e1y, -e1z, cx, cy, cz);
-    if (signbit(D)) { U = -U; V = -V; Nn = -Nn; }
-    float a = fabsf(D);
-    /* t >= tmin: for tmin == 0 (shadow rays) the comparison is Nn >= 0 and the product 0*a is not formed
-     * (it would differ only for an infinite a) */
-    int farEnough = tmin == 0.0f ? (Nn >= 0.0f) : (Nn >= tmin * a);
-    if (U >= 0.0f && V >= 0.0f && U + V <= a && farEnough && Nn * *bestD < *bestN * a) {
-        *bestN = Nn; *bestD = a;
+    /* every scaled quantity must carry the SIGN BIT of D (an exact zero with the other sign bit does not) */
+    int sD = signbit(D) != 0;
+    if ((signbit(U) != 0) != sD || (signbit(V) != 0) != sD || (signbit(Nn) != 0) != sD) return 0;
+    float a = fabsf(D), N = fabsf(Nn);
+    /* t >= tmin: for tmin == 0 (shadow rays) the sign rule is the whole test and the product 0*a is not formed */
+    int farEnough = tmin == 0.0f ? 1 : (N >= tmin * a);
+    if (fabsf(U + V) <= a && farEnough && N * *bestD < *bestN * a) {
+        *bestN = N; *bestD = a;
         return 1;
     }
     return 0;

@@ -1,0 +1,14 @@
+#!/bin/bash
+# Build an experimental copy of the library with extra nvcc flags, for A/B timing on the GPU box:
+#   bash tools/build_exp.sh NAME -DRT_SOMETHING ...   ->  tools/_build/librtcuda_NAME.so
+#   RTCUDA_LIB=tools/_build/librtcuda_NAME.so python tools/time_variants.py 1920 1080 64 3
+set -e
+NAME=$1; shift
+cd "$(dirname "$0")/../gpuraytracer_b200/csrc"
+B=../../tools/_build; mkdir -p $B
+/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo --fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
+    "$@" -cubin -o $B/pt_$NAME.cubin pathtrace.cu
+/usr/local/cuda/bin/bin2c --const --name rt_cubin_image $B/pt_$NAME.cubin > $B/pt_${NAME}_cubin.c
+echo 'const unsigned long long rt_cubin_image_size = sizeof(rt_cubin_image);' >> $B/pt_${NAME}_cubin.c
+g++ -O2 -std=c++17 -fPIC -ffp-contract=off -fno-fast-math -I/usr/local/cuda/include -pthread -shared -o $B/librtcuda_$NAME.so rtcuda.cpp host_scene.cpp -x c $B/pt_${NAME}_cubin.c -ldl 2>/dev/null
+echo $B/librtcuda_$NAME.so
