@@ -804,7 +804,16 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_wave_body<COUNT, UNROLL, R>(scene, offsets, out, p, lay, sm, counters);                        \
+        pathtrace_wave_body<COUNT, UNROLL, R, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{});  \
+    }
+/* persistent form: grid = one resident wave, (tile, sample chunk) units from an atomic counter (wave.cuh: RTTileSched) */
+#define RT_WAVE_PERSIST_ENTRY(name, COUNT, UNROLL, R, MINB)                                                      \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTTileSched ts) {                                                                                 \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        pathtrace_wave_body<COUNT, UNROLL, R, true>(scene, offsets, out, p, lay, sm, counters, ts);              \
     }
 /* warp-level path compaction, R samples per pixel per round; rtcuda.cpp adds the queue memory.
  * pathTrace_wave (R = 8) is the default kernel; exp8 / exp10 (R = 4 / 2) are kept for the tuning record
@@ -814,6 +823,8 @@ RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3)
 RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3)
 /* R = 4: half the queue memory; the library picks it when a large scene leaves room for fewer than
  * three R = 8 blocks per SM (256-sphere scene: 366 -> 482 Mpaths/s) */
+RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 8, 3)
+RT_WAVE_PERSIST_ENTRY(pathTrace_tiles4, false, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4)

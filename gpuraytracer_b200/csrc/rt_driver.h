@@ -22,7 +22,8 @@
     X(cuMemHostAlloc) X(cuMemFreeHost) X(cuMemcpyHtoD) X(cuMemcpyDtoH) X(cuMemcpyHtoDAsync) \
     X(cuMemcpyDtoHAsync) X(cuMemcpyDtoDAsync) X(cuMemsetD8) X(cuMemsetD8Async) X(cuStreamCreate) \
     X(cuStreamDestroy) X(cuStreamSynchronize) X(cuEventCreate) X(cuEventRecord) \
-    X(cuEventSynchronize) X(cuEventElapsedTime) X(cuEventDestroy) X(cuLaunchKernel)
+    X(cuEventSynchronize) X(cuEventElapsedTime) X(cuEventDestroy) X(cuLaunchKernel) \
+    X(cuOccupancyMaxActiveBlocksPerMultiprocessor)
 
 struct RTDriver {
 #define RT_DECL(name) decltype(&name) p_##name;

@@ -38,6 +38,7 @@
 #define RT_HDR_RES_X     14   /* float(camera.resolution.x)                          */
 #define RT_HDR_RES_Y     15   /* float(camera.resolution.y)                          */
 #define RT_HDR_EXPOSURE  16   /* mode B: 1 / (1.2 * 2^ev100)                         */
+#define RT_HDR_TILE_COUNTER 17 /* uint, zeroed by rt_prep_scene: next 8x4 tile of pathTrace_tiles */
 
 #define RT_ISECT_WORDS   16
 #define RT_SPHERE_WORDS   8

@@ -77,7 +77,8 @@ enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
 /* kernel variants of pathTrace (all give bit-identical images): DEFAULT picks WAVE, or SMEM when a launch
  * has fewer than 4 samples per pixel; SMEM = one thread walks one pixel's samples; CONST = the same with the
  * primitives in the constant bank; WAVE = warp-level path compaction (csrc/wave.cuh) */
-enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_COUNT_RAYS = 0x100 };
+enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16,
+       RT_VARIANT_COUNT_RAYS = 0x100 };
 
 /* What the reference hard-codes in the shader (raytrace.metal:24-25,
  * shaders.metal:644,648) plus the tile / progressive controls BASELINE.json's

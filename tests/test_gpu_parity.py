@@ -273,3 +273,34 @@ def test_camera_candidate_lists_moved_cameras(dev, scene_name):
         full = r.draw(spp=spp, variant=L.VARIANT_SMEM)                    # the kernel without candidate lists
         assert np.array_equal(full, ref), (pos, "smem")
         assert np.array_equal(img, ref), (pos, "wave", int((img != ref).sum()))
+
+
+def test_persistent_tiles_with_sample_chunks(dev, monkeypatch):
+    """pathTrace_tiles: (8x4 tile, sample chunk) units from an atomic counter; chunk c continues the running sum of
+    chunk c-1 through the output buffer.  Same bits as one pass, whatever the chunking, also with row tiles,
+    ragged sizes, accumulation onto an existing image, and as the library's own choice for a small share."""
+    W, H, spp = 200, 77, 72
+    osc = O.cornell(W, H)
+    ref, _ = O.pathtrace(osc, W, H, spp)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    for chunks in ("1", "2", "3", "9"):
+        monkeypatch.setenv("RT_TILES_CHUNKS", chunks)
+        img = r.draw(spp=spp, variant=L.VARIANT_TILES)
+        assert np.array_equal(img, ref), chunks
+    monkeypatch.delenv("RT_TILES_CHUNKS")
+    assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_TILES), ref)
+    assert np.array_equal(r.draw(spp=spp), ref)                      # default: few blocks -> the library picks tiles
+    # progressive: 40 + 32 samples accumulated, second launch chunked
+    monkeypatch.setenv("RT_TILES_CHUNKS", "2")
+    r.clear()
+    r.draw_async(spp=40, firstSample=0, accumulate=1, variant=L.VARIANT_TILES)
+    r.draw_async(spp=32, firstSample=40, accumulate=1, variant=L.VARIANT_TILES).wait_until_completed()
+    acc = r.image()
+    assert np.all(acc[..., 3] == spp) and np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3])
+    # interleaved row tiles of rank 1 of 3
+    from gpuraytracer_b200 import distributed as D
+    row0, rows, tr, ts = D.tile_params(H, 1, 3, 8)
+    mine = D.local_rows(H, 1, 3, 8)
+    off = np.ascontiguousarray(G.fill_offsets(W, 0, H, seed=1).reshape(H, W)[mine]).reshape(-1)
+    r2 = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev, row0=row0, rows=rows, offsets=off)
+    assert np.array_equal(r2.draw(spp=spp, variant=L.VARIANT_TILES, tileRows=tr, tileStride=ts), ref[mine])
