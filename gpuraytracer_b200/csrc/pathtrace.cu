@@ -77,12 +77,14 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             f3 v1 = mk(vv[1].x, vv[1].y, vv[1].z);
             f3 v2 = mk(vv[2].x, vv[2].y, vv[2].z);
             f3 e1 = v1 - v0, e2 = v2 - v0;
-            f3 nn = cross(e1, e2);                 /* un-normalised; the intersector's n is -nn (tri_accept) */
+            f3 nn = cross(e1, e2);                 /* un-normalised winding normal (shading)                  */
+            f3 ni = cross(e2, e1);                 /* the intersector's n, and e1n = v0 - v1: no unary minus  */
+            f3 e1n = v0 - v1;                      /* anywhere on the way to U, V, D, Nn (rt_detmath.h)       */
             f3 w = v0 - position;                  /* camera rays: w and Nn do not depend on the ray */
-            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = -nn.x;
-            is[4] = -nn.y; is[5] = -nn.z; is[6] = e2.x; is[7] = e2.y;
-            is[8] = e2.z; is[9] = -e1.x; is[10] = -e1.y; is[11] = -e1.z;
-            ps[0] = w.x; ps[1] = w.y; ps[2] = w.z; ps[3] = dot(w, -nn);
+            is[0] = v0.x; is[1] = v0.y; is[2] = v0.z; is[3] = ni.x;
+            is[4] = ni.y; is[5] = ni.z; is[6] = e2.x; is[7] = e2.y;
+            is[8] = e2.z; is[9] = e1n.x; is[10] = e1n.y; is[11] = e1n.z;
+            ps[0] = w.x; ps[1] = w.y; ps[2] = w.z; ps[3] = dot(w, ni);
             f3 n = normalize(nn);                                            /* sampling.metal:16-26 */
             f3 right = normalize(cross(n, mk(0.0072f, 1.0f, 0.0034f)));      /* sampling.metal:57   */
             f3 fwd = cross(right, n);                                        /* sampling.metal:61   */
@@ -140,8 +142,8 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
 /*
  * Division-free ray/triangle test in the form fixed by the arithmetic contract
  * (oracle/rt_detmath.h states the same thing for the CPU): with the
- * per-triangle constants n = -cross(e1,e2), e2, e1n = -e1 and, per ray,
- *     w = v0 - o, D = dot(d,n), Nn = dot(w,n), c = -cross(w,d), U = dot(e2,c), V = dot(e1n,c),
+ * per-triangle constants n = cross(e2,e1), e2, e1n = v0 - v1 and, per ray,
+ *     w = v0 - o, D = dot(d,n), Nn = dot(w,n), c = cross(d,w), U = dot(e2,c), V = dot(e1n,c),
  * and a = |D|, a hit needs U, V and Nn to carry the sign bit of D and
  *     |U + V| <= a, |Nn| >= tmin*a, |Nn|*bestD < bestN*a.
  * (bestN,bestD) starts at (tmax,1).  One division, bestN/bestD, after the loop.
@@ -173,7 +175,7 @@ __device__ __forceinline__ bool tri_test(float4 A, float4 B, float4 C, f3 o, f3 
     f3 w = v0 - o;
     float D = dot(d, n);
     float Nn = dot(w, n);
-    f3 c = -cross(w, d);
+    f3 c = cross(d, w);
     float U = dot(e2, c);
     float V = dot(e1n, c);
     return tri_accept(D, Nn, U, V, tmin, bestN, bestD, N_out, a_out);
@@ -185,7 +187,7 @@ __device__ __forceinline__ bool tri_test_primary(float4 P, float4 A, float4 B, f
     f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
     f3 w = mk(P.x, P.y, P.z);
     float D = dot(d, n);
-    f3 c = -cross(w, d);
+    f3 c = cross(d, w);
     float U = dot(e2, c);
     float V = dot(e1n, c);
     return tri_accept(D, P.w, U, V, tmin, bestN, bestD, N_out, a_out);
@@ -324,13 +326,13 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
             float N, a;
             {
                 float D = dot(dc, n);
-                f3 c = -cross(w, dc);
+                f3 c = cross(dc, w);
                 float U = dot(e2, c), V = dot(e1n, c);
                 if (tri_accept(D, Nn, U, V, tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
             }
             {
                 float D = dot(ds, n);
-                f3 c = -cross(w, ds);
+                f3 c = cross(ds, w);
                 float U = dot(e2, c), V = dot(e1n, c);
                 sh |= tri_accept(D, Nn, U, V, tminS, tmaxS, 1.0f, N, a);
             }
@@ -394,7 +396,7 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
             for (int r = 0; r < N; r++) {
                 float Nq, a;
                 float D = dot(d[r], n);
-                f3 c = -cross(w, d[r]);
+                f3 c = cross(d[r], w);
                 float U = dot(e2, c), V = dot(e1n, c);
                 sh[r] |= tri_accept(D, Nn, U, V, 0.0f, tmax[r], 1.0f, Nq, a);
             }
@@ -889,5 +891,19 @@ extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, 
         const uint32_t i = p[2 * k], b = p[2 * k + 1] >> 2, sl = p[2 * k + 1] & 3u;
         float r = sl == 0 ? halton_slot<0>(i, b) : sl == 1 ? halton_slot<1>(i, b) : sl == 2 ? halton_slot<2>(i, b) : halton_slot<3>(i, b);
         ((float *)out)[k] = r;
+    } else if (what == 5) {
+        /* one triangle test, the isect record built as rt_prep_scene builds it: in = v0 v1 v2 o d tmin tmax
+         * (17 floats), out = hit, distance, bestD (3 words).  For the exact-zero cases of the sign rule. */
+        const float *p = (const float *)in + 17 * k;
+        const f3 v0 = mk(p[0], p[1], p[2]), v1 = mk(p[3], p[4], p[5]), v2 = mk(p[6], p[7], p[8]);
+        const f3 o = mk(p[9], p[10], p[11]), d = mk(p[12], p[13], p[14]);
+        const f3 e1 = v1 - v0, e2 = v2 - v0, ni = cross(e2, e1), e1n = v0 - v1;
+        (void)e1;
+        const float4 A = make_float4(v0.x, v0.y, v0.z, ni.x), B = make_float4(ni.y, ni.z, e2.x, e2.y), C = make_float4(e2.z, e1n.x, e1n.y, e1n.z);
+        float N = 0.0f, a = 1.0f;
+        const bool hit = tri_test(A, B, C, o, d, p[15], p[16], 1.0f, N, a);
+        ((uint32_t *)out)[3 * k] = hit ? 1u : 0u;
+        ((float *)out)[3 * k + 1] = hit ? N / a : 0.0f;
+        ((float *)out)[3 * k + 2] = hit ? a : 0.0f;
     }
 }

@@ -185,8 +185,8 @@ RT_INLINE float rt_powf(float x, float y) {
  *
  * and per ray (o,d):
  *
- *     w  = v0 - o              D  = dot(d, n)         Nn = dot(w, n)         (n  = -(e1 x e2))
- *     c  = -cross(w, d)        U  = dot(e2, c)        V  = dot(e1n, c)
+ *     w  = v0 - o              D  = dot(d, n)         Nn = dot(w, n)         (n = e2 x e1, e1n = v0 - v1)
+ *     c  = cross(d, w)         U  = dot(e2, c)        V  = dot(e1n, c)
  *     a = |D|
  *
  * which are the classic quantities scaled by the determinant: (u,v,t) =
@@ -201,9 +201,13 @@ RT_INLINE float rt_powf(float x, float y) {
  * three-input logic operations and one integer compare for all three quantities, where flipping and
  * comparing each one costs three more issue slots per test.  The two forms differ only for an exact
  * zero whose sign bit is not D's.  An exact zero of U or V -- a ray through an edge -- comes out of a
- * cancellation as +0, and with n and c negated as above D is POSITIVE where the ray meets the side the
+ * cancellation as +0, and with n = e2 x e1, c = d x w D is POSITIVE where the ray meets the side the
  * winding normal e1 x e2 points to: there both triangles of a shared edge accept and the lower id wins,
- * as with the inclusive comparison; on a back face such a ray is accepted by neither.)
+ * as with the inclusive comparison; on a back face such a ray is accepted by neither.  Because the sign
+ * of such a zero now decides, NO quantity on the way to U, V, D, Nn is formed by a unary minus: a compiler
+ * may move a negation through a product or into the logic operation that tests the sign bit, which is
+ * exact for every value except the sign of an exact zero -- and exact zeros do occur, about twice per
+ * 1e8 paths of the Cornell frame.)
  * D == 0 can never pass (|Nn|*bestD < bestN*0 is false).  The reported
  * distance is the single division bestN/bestD after the loop.
  * Cost: 21 multiply/add instructions per test (w 3, D 3, Nn 3, c 6, U 3, V 3),
@@ -229,15 +233,14 @@ RT_INLINE int rt_triangle_test(const float *v0, const float *v1, const float *v2
     float e1x = v1[0] - v0[0], e1y = v1[1] - v0[1], e1z = v1[2] - v0[2];
     float e2x = v2[0] - v0[0], e2y = v2[1] - v0[1], e2z = v2[2] - v0[2];
     float nx, ny, nz, cx, cy, cz;
-    rt_cross3(e1x, e1y, e1z, e2x, e2y, e2z, &nx, &ny, &nz);
-    nx = -nx; ny = -ny; nz = -nz;                           /* n = -(e1 x e2) */
+    float e1nx = v0[0] - v1[0], e1ny = v0[1] - v1[1], e1nz = v0[2] - v1[2];
+    rt_cross3(e2x, e2y, e2z, e1x, e1y, e1z, &nx, &ny, &nz);             /* n = e2 x e1 */
     float wx = v0[0] - o[0], wy = v0[1] - o[1], wz = v0[2] - o[2];
     float D  = rt_dot3(d[0], d[1], d[2], nx, ny, nz);
     float Nn = rt_dot3(wx, wy, wz, nx, ny, nz);
-    rt_cross3(wx, wy, wz, d[0], d[1], d[2], &cx, &cy, &cz);
-    cx = -cx; cy = -cy; cz = -cz;                           /* c = -(w x d) */
+    rt_cross3(d[0], d[1], d[2], wx, wy, wz, &cx, &cy, &cz);             /* c = d x w */
     float U = rt_dot3(e2x, e2y, e2z, cx, cy, cz);
-    float V = rt_dot3(-e1x, -e1y, -e1z, cx, cy, cz);
+    float V = rt_dot3(e1nx, e1ny, e1nz, cx, cy, cz);
     /* every scaled quantity must carry the SIGN BIT of D (an exact zero with the other sign bit does not) */
     int sD = signbit(D) != 0;
     if ((signbit(U) != 0) != sD || (signbit(V) != 0) != sD || (signbit(Nn) != 0) != sD) return 0;

@@ -304,3 +304,35 @@ def test_persistent_tiles_with_sample_chunks(dev, monkeypatch):
     off = np.ascontiguousarray(G.fill_offsets(W, 0, H, seed=1).reshape(H, W)[mine]).reshape(-1)
     r2 = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev, row0=row0, rows=rows, offsets=off)
     assert np.array_equal(r2.draw(spp=spp, variant=L.VARIANT_TILES, tileRows=tr, tileStride=ts), ref[mine])
+
+
+def test_triangle_test_exact_zero_cases(dev):
+    """The sign rule makes the sign bit of an exact zero of U, V, Nn or D decide (rays through edges and vertices,
+    origins in the triangle's plane, rays in the plane).  Small-integer triangles and rays produce such zeros in
+    bulk: the device test must agree with the oracle's on every one, bit for bit (a compiler that moves a negation
+    through the arithmetic breaks exactly these -- DESIGN.md 3)."""
+    rng = np.random.default_rng(7)
+    n = 60000
+    cases = np.zeros((n, 17), np.float32)
+    cases[:, 0:9] = rng.integers(-3, 4, (n, 9))                  # v0 v1 v2 on the integer lattice
+    cases[:, 9:12] = rng.integers(-4, 5, (n, 3))                 # origin
+    tgt = rng.integers(-3, 4, (n, 3)).astype(np.float32)         # aim at lattice points: edges, vertices, planes
+    half = rng.random(n) < 0.5
+    tgt[half] = (cases[half, 0:3] + cases[half, 3:6]) * np.float32(0.5)   # ... and at edge midpoints
+    cases[:, 12:15] = tgt - cases[:, 9:12]
+    cases[:, 15] = np.where(rng.random(n) < 0.5, 0.0, 1e-3)      # shadow-ray and camera-ray tmin
+    cases[:, 16] = np.where(rng.random(n) < 0.3, 1.0, 1000.0)    # tmax == the hit distance for many
+    out = np.zeros((n, 3), np.uint32)
+    debug_eval(dev, 5, cases.reshape(-1), out)
+    hits = 0
+    dist = C.c_float(); pid = C.c_uint32()
+    for k in range(n):
+        verts = np.zeros((3, 4), np.float32); verts[:, :3] = cases[k, 0:9].reshape(3, 3)
+        o = np.ascontiguousarray(cases[k, 9:12]); d = np.ascontiguousarray(cases[k, 12:15])
+        hit = O.lib.rt_oracle_intersect(O.vp(verts), 1, None, 0, O.vp(o), O.vp(d), C.c_float(float(cases[k, 15])),
+                                        C.c_float(float(cases[k, 16])), 0, C.byref(dist), C.byref(pid))
+        assert hit == int(out[k, 0]), (k, cases[k].tolist())
+        if hit:
+            hits += 1
+            assert np.float32(dist.value).view(np.uint32) == out[k, 1], (k, cases[k].tolist())
+    assert hits > n // 20            # the set does exercise accepted hits, not only rejections
