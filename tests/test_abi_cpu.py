@@ -82,3 +82,31 @@ def test_sphere_scene_is_sane():
     assert np.all(np.abs(c) + r[:, None] < 2.5)          # inside the room
     d = np.linalg.norm(c[:, None] - c[None], axis=-1) + np.eye(256) * 9
     assert np.all(d > r[:, None] + r[None])              # no two spheres overlap
+
+
+def test_png_writer_of_the_cpp_host_round_trips(tmp_path):
+    """image.swift:102-157 mirror (csrc/host_renderer.cpp): RGBA8 -> PNG with stored deflate blocks, read back by PIL."""
+    import ctypes as C
+    from PIL import Image
+    from gpuraytracer_b200._lib import lib
+    rng = np.random.default_rng(5)
+    for (w, h) in ((1, 1), (37, 19), (800, 100)):       # 800x100x4+100 bytes: more than one 65535-byte deflate block
+        px = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        path = str(tmp_path / f"t_{w}x{h}.png").encode()
+        lib.rtHostSavePixelArrayToImage.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
+        assert lib.rtHostSavePixelArrayToImage(px.ctypes.data, w, h, path) == 0
+        back = np.asarray(Image.open(path.decode()))
+        assert back.shape == (h, w, 4) and np.array_equal(back, px)
+
+
+def test_rtrace_executable_fails_loudly_without_a_gpu():
+    """The C++ host of the build (RTrace/main.swift over the C ABI): without a driver it reports and exits 1, no image."""
+    import os
+    import subprocess
+    import torch
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpuraytracer_b200", "rtrace")
+    assert os.path.exists(exe)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: covered by the gpu tests")
+    r = subprocess.run([exe, "/tmp/should_not_exist.png", "--spp", "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "libcuda" in r.stderr and not os.path.exists("/tmp/should_not_exist.png")

@@ -336,3 +336,25 @@ def test_triangle_test_exact_zero_cases(dev):
             hits += 1
             assert np.float32(dist.value).view(np.uint32) == out[k, 1], (k, cases[k].tolist())
     assert hits > n // 20            # the set does exercise accepted hits, not only rejections
+
+
+def test_rtrace_executable_writes_the_oracles_image(dev, tmp_path):
+    """gpuraytracer_b200/rtrace = RTrace/main.swift over the C ABI (csrc/host_renderer.cpp mirrors renderer.swift and
+    image.swift): its PNG must be the oracle's image through the oracle's tone map, +-1 LSB (powf on the device)."""
+    import os
+    import subprocess
+    from PIL import Image
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpuraytracer_b200", "rtrace")
+    W, H, spp = 160, 120, 16
+    out = str(tmp_path / "out.png")
+    r = subprocess.run([exe, out, "--width", str(W), "--height", str(H), "--spp", str(spp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Image saved to" in r.stdout and "Render completed in" in r.stdout
+    png = np.asarray(Image.open(out))
+    ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
+    want = np.zeros((H, W, 4), np.uint8)
+    O.lib.rt_oracle_tonemap_rgba8(O.vp(np.ascontiguousarray(ref)), O.vp(want), C.c_uint64(W * H))
+    assert png.shape == (H, W, 4) and np.all(png[..., 3] == 255)
+    assert int(np.abs(png[..., :3].astype(int) - want[..., :3].astype(int)).max()) <= 1
+    # unknown option -> usage error, no crash
+    assert subprocess.run([exe, "--nonsense"], capture_output=True).returncode == 2
