@@ -116,24 +116,47 @@ def oracle_sample(a, rows_per_tile=TILE_ROWS, tiles=None, nthreads=0):
 
 
 def run_reference(a, rank):
-    """--impl reference: the reference path's CPU restatement (oracle port; the reference has no CPU
-    code of its own and its Metal shaders cannot run here) on all host cores, bounded sample per step."""
+    """--impl reference: the reference's own kernel source on the host cores.  oracle/_ref is RTrace/raytrace.metal +
+    sampling.metal, UNMODIFIED, compiled as C++ (oracle/ref_driver_a.cpp; the closed-source Metal ray query is the
+    brute-force intersector of oracle/rt_detmath.h) -- so it runs at the shader's literal 400 spp / 3 bounces
+    (raytrace.metal:24-25); Mpaths/s does not depend on the sample count.  Without the prebuilt library the C
+    restatement (oracle port, bit-identical to it) is timed instead.  All host threads, bounded sample per step."""
     if rank != 0:
         return
-    tiles = [H // 2 // TILE_ROWS * TILE_ROWS]          # 8 rows through the middle of the frame
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    import ref_lib as R
+    ref = R.load() if a.bounces == 3 else None
+    r0 = H // 2 // TILE_ROWS * TILE_ROWS               # 8 rows through the middle of the frame
+    cores = O.lib.rt_oracle_max_threads()
+    if ref is not None:
+        sc, off, spp, kind = O.cornell(W, H), O.offsets(W, 0, H, seed=1), 400, "reference"
+
+        def one():
+            t0 = time.perf_counter()
+            R.pathtrace(ref, sc, W, H, off, row0=r0, rows=TILE_ROWS)
+            return W * TILE_ROWS * spp, time.perf_counter() - t0
+    else:
+        spp, kind = a.spp, "port"
+
+        def one():
+            _, p, dt, _ = oracle_sample(a, tiles=[r0])
+            return p, dt
     for _ in range(a.warmup):
-        oracle_sample(a, tiles=tiles)
+        one()
     t, paths = 0.0, 0
     for _ in range(a.steps):
-        _, p, dt, cores = oracle_sample(a, tiles=tiles)
+        p, dt = one()
         t += dt; paths += p
     v = paths / t / 1e6
-    sample = f"rows {tiles[0]}..{tiles[0] + 7} x {W} px x {a.spp} spp per step ({paths // a.steps} paths), OpenMP {cores} threads"
+    what = ("oracle/_ref = the reference's raytrace.metal + sampling.metal compiled as C++, at the shader's literal 400 spp"
+            if kind == "reference" else "C restatement of the shaders (oracle port)")
+    sample = f"rows {r0}..{r0 + 7} x {W} px x {spp} spp per step ({paths // a.steps} paths), {what}, OpenMP {cores} threads"
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus,
                       "steps": a.steps, "warmup": a.warmup, "ms_per_step": t / a.steps * 1e3,
                       "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                       "data": "synthetic", "config": workload(a),
-                      "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                      "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
                       "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                       "gpu_launches": 0}))
 

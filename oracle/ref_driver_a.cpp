@@ -36,9 +36,11 @@ extern "C" int rt_ref_pathtrace(const void *cameras, const void *materials, cons
     accel.vertices = (const float *)vertices;
     accel.triangleCount = numTriangles;
     float debug[4] = { 0, 0, 0, 0 };
+    // jobs of 32 grid points of one row, so that a few rows still keep every core busy
+    const int chunks = (width + 31) / 32;
 #pragma omp parallel for schedule(dynamic, 1)
-    for (int y = row0; y < row0 + rows; y++)
-        for (int x = 0; x < width; x++)
+    for (int job = 0; job < rows * chunks; job++)
+        for (int y = row0 + job / chunks, x = (job % chunks) * 32, xe = x + 32 < width ? x + 32 : width; x < xe; x++)
             ref_a::pathTrace((const ref_a::CameraGPU *)cameras, (const ref_a::MaterialGPU *)materials,
                              (const ref_a::SquareLightGPU *)lights, (const float3 *)vertices,
                              outputTexture, randomTexture, accel, debug, uint3((uint)x, (uint)y, 0u));

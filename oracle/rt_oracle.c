@@ -263,12 +263,15 @@ int rt_oracle_pathtrace(const CameraGPU *cameras, const MaterialGPU *materials,
 #pragma omp parallel num_threads(nthreads)
     {
         uint64_t cnt[RT_CNT_COUNT] = { 0 };
+        /* jobs of 32 pixels of one row, so that a few rows still keep every core busy */
+        const int chunks = (W + 31) / 32;
 #pragma omp for schedule(dynamic, 1)
-        for (int ly = 0; ly < p->rows; ly++) {
+        for (int job = 0; job < p->rows * chunks; job++) {
+            const int ly = job / chunks, xb = (job % chunks) * 32, xe = xb + 32 < W ? xb + 32 : W;
             const uint32_t iy = p->tileRows
                 ? (uint32_t)p->row0 + ((uint32_t)ly / p->tileRows) * p->tileStride + ((uint32_t)ly % p->tileRows)
                 : (uint32_t)(p->row0 + ly);
-            for (int x = 0; x < W; x++) {
+            for (int x = xb; x < xe; x++) {
                 const size_t px = (size_t)ly * W + x;
                 const uint32_t offset = offsets[px];          /* raytrace.metal:37 */
                 float *o = out + px * 4;

@@ -448,12 +448,14 @@ int rt_oracle_drawtriangle(const CameraGPU *cameras, const MaterialGPU *material
     {
         uint64_t cnt[RT_CNT_COUNT] = { 0 };
         ctx_t c = { cameras, materials, lights, vertices, p->numTriangles, cnt };
+        const int chunks = (W + 15) / 16;        /* jobs of 16 pixels of one row */
 #pragma omp for schedule(dynamic, 1)
-        for (int ly = 0; ly < p->rows; ly++) {
+        for (int job = 0; job < p->rows * chunks; job++) {
+            const int ly = job / chunks, xb = (job % chunks) * 16, xe = xb + 16 < W ? xb + 16 : W;
             const uint32_t iy = p->tileRows
                 ? (uint32_t)p->row0 + ((uint32_t)ly / p->tileRows) * p->tileStride + ((uint32_t)ly % p->tileRows)
                 : (uint32_t)(p->row0 + ly);
-            for (int x = 0; x < W; x++) {
+            for (int x = xb; x < xe; x++) {
                 const size_t px = (size_t)ly * W + x;
                 /* shaders.metal:642: threads outside the camera resolution do nothing */
                 if (x >= cameras[0].resolution.x || (int)iy >= cameras[0].resolution.y) continue;
