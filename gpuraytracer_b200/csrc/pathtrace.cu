@@ -801,12 +801,12 @@ RT_PATHTRACE_ENTRY(pathTrace_const, true, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
 #include "wave.cuh"
-#define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB)                                                              \
+#define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB, SPATIAL)                                                            \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_wave_body<COUNT, UNROLL, R, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{});  \
+        pathtrace_wave_body<COUNT, UNROLL, R, false, SPATIAL>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
     }
 /* persistent form: grid = one resident wave, (tile, sample chunk) units from an atomic counter (wave.cuh: RTTileSched) */
 #define RT_WAVE_PERSIST_ENTRY(name, COUNT, UNROLL, R, MINB)                                                      \
@@ -815,24 +815,27 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
          const RTTileSched ts) {                                                                                 \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_wave_body<COUNT, UNROLL, R, true>(scene, offsets, out, p, lay, sm, counters, ts);              \
+        pathtrace_wave_body<COUNT, UNROLL, R, true, false>(scene, offsets, out, p, lay, sm, counters, ts);       \
     }
 /* warp-level path compaction, R samples per pixel per round; rtcuda.cpp adds the queue memory.
  * pathTrace_wave (R = 8) is the default kernel; exp8 / exp10 (R = 4 / 2) are kept for the tuning record
  * (profiles/r01h_variants_wave.txt), like the unroll x occupancy sweep of pathTrace_smem before them
  * (profiles/r01c_variants.txt: all within 2 %). */
-RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3)
-RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3)
+RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3, false)
+RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3, false)
 /* R = 4: half the queue memory; the library picks it when a large scene leaves room for fewer than
  * three R = 8 blocks per SM (256-sphere scene: 366 -> 482 Mpaths/s) */
+/* fewer samples per launch than a round has slots: G = R / spp tiles side by side per warp (wave.cuh: SPATIAL) */
+RT_WAVE_ENTRY(pathTrace_wide, false, 4, 8, 3, true)
+RT_WAVE_ENTRY(pathTrace_wide4, false, 4, 4, 4, true)
 RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 8, 3)
 RT_WAVE_PERSIST_ENTRY(pathTrace_tiles4, false, 4, 4, 4)
-RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4)
-RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4)
-RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4)
-RT_WAVE_ENTRY(pathTrace_exp6, false, 4, 6, 4)
-RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4)
-RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2)
+RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4, false)
+RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4, false)
+RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4, false)
+RT_WAVE_ENTRY(pathTrace_exp6, false, 4, 6, 4, false)
+RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4, false)
+RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
 
 #include "modeb.cuh"
 

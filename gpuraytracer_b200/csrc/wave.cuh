@@ -48,7 +48,7 @@ struct WaveSmem {
     static constexpr uint32_t WORDS_PER_WARP = (RT_WAVE_FIELDS + RT_WAVE_RES) * CAP;
 };
 
-template <bool COUNT, int UNROLL, int R, bool PERSIST>
+template <bool COUNT, int UNROLL, int R, bool PERSIST, bool SPATIAL>
 __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                     float4 *__restrict__ out, const RTLaunchParams p,
                                                     const RTSceneLayout lay, float *sm,
@@ -91,6 +91,11 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
      * staging above), so an SM is busy until the last tile is handed out; otherwise the tile is the
      * warp's place in the block's 16x8 pixels. */
     const uint32_t tilesX = ((uint32_t)p.width + 7u) >> 3, tilesY = ((uint32_t)p.rows + 3u) >> 2;
+    /* SPATIAL (launches with fewer samples per pixel than the R slots of a round, progressive rendering): the
+     * warp takes G = R / spp tiles side by side (sub-tile t = pixels x + 8t) and a round's slot j is sample
+     * j % spp of sub-tile j / spp, so the queue is as full as with R samples of one tile.  One round per warp;
+     * each pixel's samples are consecutive slots, added in order in phase 3. */
+    const uint32_t G = SPATIAL ? max(1u, (uint32_t)R / max(p.spp, 1u)) : 1u;
     for (;;) {
     uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
     if (PERSIST) {
@@ -103,8 +108,9 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
         kBegin = chunk * ts.chunkSpp; kEnd = min(p.spp, kBegin + ts.chunkSpp);
         x0 = (tile % tilesX) * 8u; ly0 = (tile / tilesX) * 4u;
     } else {
-        x0 = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
+        x0 = (blockIdx.x * RT_BLOCK_W + (warp & 1) * 8) * G; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
     }
+    if (SPATIAL) kEnd = G * p.spp;                 /* one round: G sub-tiles x spp samples <= R slots */
     const uint32_t x = x0 + (lane & 7), ly = ly0 + (lane >> 3);
     /* out-of-image lanes stay in the warp (they help consume the queue) but own no pixel */
     const bool owns = x < (uint32_t)p.width && ly < (uint32_t)p.rows;
@@ -120,7 +126,8 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     {
         CameraFrame cf = { cam_o, cam_u, cam_v, cam_w, halfW, halfH, resX, resY };
         const int big = 0x3fffffff;
-        const int x0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), x1 = __reduce_max_sync(0xffffffffu, owns ? (int)x : -big);
+        const int xr = SPATIAL ? (int)min(x + 8u * (G - 1u), (uint32_t)p.width - 1u) : (int)x;      /* rightmost sub-tile */
+        const int x0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), x1 = __reduce_max_sync(0xffffffffu, owns ? xr : -big);
         const int y0 = __reduce_min_sync(0xffffffffu, owns ? (int)y : big), y1 = __reduce_max_sync(0xffffffffu, owns ? (int)y : -big);
         camera_candidates(sc, cf, lay.T, lay.S, (float)x0 - 1.0f, (float)x1 + 2.0f, (float)y0 - 1.0f, (float)y1 + 2.0f,
                           cullT, mwT, cullS, mwS, lane);
@@ -136,7 +143,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
         }
         __syncwarp();
         if (owns) { float4 o = __ldcg(out + pix); lum = mk(o.x, o.y, o.z); }
-    } else if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
+    } else if (!SPATIAL && p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 
 #pragma unroll 1
     for (uint32_t k0 = kBegin; k0 < kEnd; k0 += R) {
@@ -152,21 +159,34 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
             uint32_t id[2] = { 0u, 0u }, idx[2];
             f3 hp[2], r0[2];
             hp[0] = hp[1] = r0[0] = r0[1] = mk(0.0f, 0.0f, 0.0f);
-            idx[0] = offset + (p.firstSample + k0 + s); idx[1] = idx[0] + 1u;
-            if (owns) {
+            bool own[2] = { owns, owns };
+            float fxq[2] = { fx, fx };
+            if (SPATIAL) {
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    const uint32_t j = s + q, t = j / p.spp, xt = x + 8u * t;
+                    own[q] = owns && xt < (uint32_t)p.width && j < nround;
+                    fxq[q] = (float)(int)xt;
+                    idx[q] = (own[q] ? offsets[pix + 8u * t] : 0u) + (p.firstSample + (j - t * p.spp));
+                }
+            } else {
+                idx[0] = offset + (p.firstSample + k0 + s); idx[1] = idx[0] + 1u;
+            }
+            if (own[0] || own[1]) {
                 f3 rd[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
                     float jx = halton<0>(idx[q]), jy = halton<1>(idx[q]);
-                    float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
+                    float sx = ((fxq[q] + jx) / resX) * 2.0f - 1.0f;
                     float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
                     rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
                 }
                 bool hit[2]; float dist[2];
                 /* (an odd last pass traces its second ray for nothing: one code path, smaller kernel) */
                 closest_primary2_list(sc, cullT, mwT, cullS, mwS, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
-                hit[1] = hit[1] && two;
-                if (COUNT) cnt.closest += two ? 2u : 1u;
+                hit[0] = hit[0] && own[0];
+                hit[1] = hit[1] && two && own[1];
+                if (COUNT) cnt.closest += SPATIAL ? (own[0] ? 1u : 0u) + (two && own[1] ? 1u : 0u) : (two ? 2u : 1u);
 #pragma unroll
                 for (int q = 0; q < 2; q++) {
                     if (hit[q]) {
@@ -321,12 +341,31 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
 
         /* ---- 3. in-order accumulation, raytrace.metal:103 ---------------------------------- */
         __syncwarp();
-        for (uint32_t s = 0; s < nround; s++)
-            lum = lum + mk(res[0 * CAP + s * 32u + lane], res[1 * CAP + s * 32u + lane], res[2 * CAP + s * 32u + lane]);
+        if (SPATIAL) {
+            for (uint32_t t = 0; t < G; t++) {
+                const uint32_t xt = x + 8u * t;
+                if (!(owns && xt < (uint32_t)p.width)) continue;
+                const size_t pt = pix + 8u * t;
+                f3 l = mk(0.0f, 0.0f, 0.0f);
+                if (p.accumulate) { float4 o = out[pt]; l = mk(o.x, o.y, o.z); }
+                for (uint32_t s = t * p.spp; s < (t + 1u) * p.spp; s++)
+                    l = l + mk(res[0 * CAP + s * 32u + lane], res[1 * CAP + s * 32u + lane], res[2 * CAP + s * 32u + lane]);
+                float4 o;
+                if (p.accumulate) o = make_float4(l.x, l.y, l.z, (float)(p.firstSample + p.spp));
+                else { float samples = (float)p.spp; o = make_float4(l.x / samples, l.y / samples, l.z / samples, 1.0f); }
+                out[pt] = o;
+                if (COUNT) paths += p.spp;
+            }
+        } else {
+            for (uint32_t s = 0; s < nround; s++)
+                lum = lum + mk(res[0 * CAP + s * 32u + lane], res[1 * CAP + s * 32u + lane], res[2 * CAP + s * 32u + lane]);
+        }
         __syncwarp();
     }
 
-    if (PERSIST && kEnd < p.spp) {
+    if (SPATIAL) {
+        /* stored per sub-tile above */
+    } else if (PERSIST && kEnd < p.spp) {
         /* not the last chunk: leave the running sum for the next one and publish it */
         if (owns) __stcg(out + pix, make_float4(lum.x, lum.y, lum.z, 0.0f));
         __threadfence();
@@ -342,7 +381,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
         }
         out[pix] = o;
     }
-    if (COUNT && owns) paths += kEnd - kBegin;
+    if (COUNT && owns && !SPATIAL) paths += kEnd - kBegin;
     if (!PERSIST) break;
     }
 #undef QF

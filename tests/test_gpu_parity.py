@@ -358,3 +358,30 @@ def test_rtrace_executable_writes_the_oracles_image(dev, tmp_path):
     assert int(np.abs(png[..., :3].astype(int) - want[..., :3].astype(int)).max()) <= 1
     # unknown option -> usage error, no crash
     assert subprocess.run([exe, "--nonsense"], capture_output=True).returncode == 2
+
+
+def test_wide_kernel_few_samples_per_launch(dev):
+    """pathTrace_wide (launches with fewer samples than a round has slots): a warp takes 8 / spp tiles side by side.
+    Same bits as the oracle for every spp < 8, ragged widths, row tiles, and as a progressive accumulation of
+    1-spp frames (the library's default for them)."""
+    W, H = 203, 61                      # 203 = 25 tiles + 3 pixels: ragged against every G
+    osc = O.cornell(W, H)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    for spp in (1, 2, 3, 4, 5, 7):
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_WIDE), ref), spp
+        assert np.array_equal(r.draw(spp=spp), ref), spp           # default picks the wide form below 8 spp
+    # progressive: 12 frames of 1 spp == one 12-spp launch, bit for bit
+    ref, _ = O.pathtrace(osc, W, H, 12)
+    r.clear()
+    for f in range(12):
+        cmd = r.draw_async(spp=1, firstSample=f, accumulate=1)
+    cmd.wait_until_completed()
+    acc = r.image()
+    assert np.all(acc[..., 3] == 12) and np.array_equal(acc[..., :3] / np.float32(12), ref[..., :3])
+    # spheres scene (R = 4 there: wide4) and a row tile
+    W2, H2 = 120, 40
+    ref, _ = O.pathtrace(O.spheres(W2, H2), W2, H2, 2, row0=8, rows=24)
+    off = G.fill_offsets(W2, 8, 24, seed=1)
+    r2 = G.Renderer(G.init_sphere_scene(W2, H2), W2, H2, device=dev, row0=8, rows=24, offsets=off)
+    assert np.array_equal(r2.draw(spp=2), ref)
