@@ -65,7 +65,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         scene[RT_HDR_RES_X] = (float)resx;
         scene[RT_HDR_RES_Y] = (float)resy;
         scene[RT_HDR_EXPOSURE] = 1.0f / (1.2f * pow_det(2.0f, ev100));   /* cameraExposure, shaders.metal:145-150 */
-        for (int i = RT_HDR_EXPOSURE + 1; i < RT_HDR_WORDS; i++) scene[i] = 0.0f;
+        for (int i = RT_HDR_EXPOSURE + 1; i < RT_HDR_WORDS; i++) if (i != RT_HDR_PAIRED) scene[i] = 0.0f;
     }
     for (uint32_t i = tid; i < lay.Tp; i += nth) {
         float *is = scene + lay.isect + RT_ISECT_WORDS * i;
@@ -127,6 +127,17 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             pp[0] = 0.0f; pp[1] = -3.0e18f; pp[2] = 0.0f; pp[3] = 9.0e36f;
             for (int k = 0; k < RT_SSHADE_ROWS; k++) sh[k * lay.Sp] = 0.0f;
         }
+    }
+    {
+        /* is every triangle 2k+1 on the v0 of triangle 2k, bit for bit?  (PAIRED loops; padding pairs are all zero) */
+        int ok = (lay.T % 2u) == 0u;
+        for (uint32_t i = 2u * tid + 1u; i < lay.T; i += 2u * nth) {
+            const uint32_t *a = (const uint32_t *)((const SimdF3 *)vertices + 3 * (i - 1u));
+            const uint32_t *b = (const uint32_t *)((const SimdF3 *)vertices + 3 * i);
+            ok = ok && a[0] == b[0] && a[1] == b[1] && a[2] == b[2];
+        }
+        ok = __syncthreads_and(ok);
+        if (tid == 0) ((uint32_t *)scene)[RT_HDR_PAIRED] = ok ? 1u : 0u;
     }
     for (uint32_t l = tid; l < lay.L; l += nth) {
         const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
@@ -267,16 +278,32 @@ __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o
     return best != 0xffffffffu;
 }
 
-template <bool CONST_BANK, int UNROLL>
+/*
+ * PAIRED (all loops below): rt_prep_scene found that every triangle 2k+1 has bit for bit the v0 of triangle 2k
+ * (a quad cut in two, the way scene.swift builds every wall, box face and the light).  Then w = v0 - o and
+ * c = cross(d, w) of the second triangle ARE the first one's -- same operands, same operations -- and are not
+ * computed again: 9 of the 21 FP32 instructions of every second test.  Nothing is approximated; the results are
+ * the unpaired loop's bit for bit (tests run both).
+ */
+template <bool CONST_BANK, int UNROLL, bool PAIRED = false>
 __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax) {
+    static_assert(!PAIRED || UNROLL % 2 == 0, "pairs must not straddle an unrolled block");
     bool hit = false;
 #pragma unroll 1
     for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+        f3 w = mk(0.0f, 0.0f, 0.0f), c = w;
 #pragma unroll
         for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
             float N, a;
-            hit |= tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, tmax, 1.0f, N, a);
+            if (!PAIRED) {
+                hit |= tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, tmax, 1.0f, N, a);
+            } else {
+                const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+                const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+                if (!(u & 1)) { w = mk(A.x, A.y, A.z) - o; c = cross(d, w); }
+                hit |= tri_accept(dot(d, n), dot(w, n), dot(e2, c), dot(e1n, c), tmin, tmax, 1.0f, N, a);
+            }
         }
     }
     if (sc.S) {
@@ -307,33 +334,37 @@ __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3
  * dependency chains in flight.  Same operations on the same operands as tri_test, so the
  * results are bit-identical to closest_hit + any_hit.  (Spheres: m = o - c and C are shared.)
  */
-template <bool CONST_BANK, int UNROLL>
+template <bool CONST_BANK, int UNROLL, bool PAIRED = false>
 __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
                                          f3 dc, float tminC, float tmaxC, float &dist, uint32_t &id,
                                          f3 ds, float tminS, float tmaxS, bool &shadowed) {
+    static_assert(!PAIRED || UNROLL % 2 == 0, "pairs must not straddle an unrolled block");
     float bestN = tmaxC, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
     bool sh = false;
 #pragma unroll 1
     for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+        f3 w = mk(0.0f, 0.0f, 0.0f), cC = w, cS = w;
 #pragma unroll
         for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
             const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
-            const f3 v0 = mk(A.x, A.y, A.z), n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
-            const f3 w = v0 - o;
+            const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+            if (!PAIRED || !(u & 1)) {                 /* PAIRED: the second triangle of a pair has the same v0 */
+                w = mk(A.x, A.y, A.z) - o;
+                cC = cross(dc, w);
+                cS = cross(ds, w);
+            }
             const float Nn = dot(w, n);
             float N, a;
             {
                 float D = dot(dc, n);
-                f3 c = cross(dc, w);
-                float U = dot(e2, c), V = dot(e1n, c);
+                float U = dot(e2, cC), V = dot(e1n, cC);
                 if (tri_accept(D, Nn, U, V, tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
             }
             {
                 float D = dot(ds, n);
-                f3 c = cross(ds, w);
-                float U = dot(e2, c), V = dot(e1n, c);
+                float U = dot(e2, cS), V = dot(e1n, cS);
                 sh |= tri_accept(D, Nn, U, V, tminS, tmaxS, 1.0f, N, a);
             }
         }

@@ -38,6 +38,7 @@
 #define RT_HDR_RES_X     14   /* float(camera.resolution.x)                          */
 #define RT_HDR_RES_Y     15   /* float(camera.resolution.y)                          */
 #define RT_HDR_EXPOSURE  16   /* mode B: 1 / (1.2 * 2^ev100)                         */
+#define RT_HDR_PAIRED    18   /* uint: every triangle 2k+1 shares v0 with triangle 2k (rt_prep_scene)   */
 #define RT_HDR_TILE_COUNTER 17 /* uint, zeroed by rt_prep_scene: next 8x4 tile of pathTrace_tiles */
 
 #define RT_ISECT_WORDS   16

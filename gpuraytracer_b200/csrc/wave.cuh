@@ -83,6 +83,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     const float halfW = sm[RT_HDR_HALF_W], halfH = sm[RT_HDR_HALF_H];
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
+    const bool paired = ((const uint32_t *)sm)[RT_HDR_PAIRED] != 0u;           /* quads cut in two: pathtrace.cu, PAIRED */
     Counters cnt = { 0u, 0u, 0u };
     unsigned long long paths = 0ull;
 
@@ -276,8 +277,13 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                         f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
                         lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
                         bool shadowed;
-                        if (cont) hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
-                        else shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
+                        if (paired) {                                                           /* warp-uniform, per launch */
+                            if (cont) hitC = dual_hit<false, UNROLL, true>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
+                            else shadowed = any_hit<false, UNROLL, true>(sc, P, ldir, 0.0f, ldist - 1e-3f);
+                        } else {
+                            if (cont) hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
+                            else shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
+                        }
                         if (!shadowed) acc = acc + lightColor * color;                          /* :88 */
                     } else {
                         uint32_t l = 0;

@@ -385,3 +385,25 @@ def test_wide_kernel_few_samples_per_launch(dev):
     off = G.fill_offsets(W2, 8, 24, seed=1)
     r2 = G.Renderer(G.init_sphere_scene(W2, H2), W2, H2, device=dev, row0=8, rows=24, offsets=off)
     assert np.array_equal(r2.draw(spp=2), ref)
+
+
+def test_paired_and_unpaired_triangle_loops_agree(dev):
+    """rt_prep_scene flags a scene whose triangles 2k, 2k+1 share v0 bit for bit (quads cut in two); the wave kernel
+    then reuses w and cross(d, w) for the second triangle of each pair.  Breaking the pairing (one vertex moved by
+    one ulp, or an odd triangle count) must switch to the plain loops, and both must match the oracle."""
+    W, H, spp = 128, 96, 8
+    for mode in ("paired", "ulp", "odd"):
+        osc = O.cornell(W, H); gsc = G.init_cornell_box(W, H)
+        T = 36
+        if mode == "ulp":
+            for sc_bytes in (osc["vertices"], gsc.vertices):
+                v = sc_bytes.view(np.uint32)
+                v[3 * 4 * 5 + 0] += 1            # triangle 5, vertex 0, x: one ulp off its partner's v0
+        if mode == "odd":
+            T = 35                               # drop the last light triangle: T odd -> not paired
+            osc["vertices"] = osc["vertices"][:T * 48].copy(); osc["materials"] = osc["materials"][:T * 48].copy(); osc["T"] = T
+            gsc.vertices = gsc.vertices[:T * 48].copy(); gsc.materials = gsc.materials[:T * 48].copy(); gsc.num_triangles = T
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        r = G.Renderer(gsc, W, H, device=dev)
+        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_WAVE), ref), mode
+        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SMEM), ref), mode
