@@ -142,7 +142,10 @@ using namespace rt;
 __device__ __noinline__ bool closest_b(const float4 *base, uint32_t T4, uint32_t Treal, f3 o, f3 d, float tmin, float tmax,
                                        float &dist, uint32_t &id) {
     SceneRef<false> sc;
-    sc.base = base; sc.T = T4; sc.S = 0; sc.Treal = Treal; sc.sph = 0;
+    sc.base = base; sc.S = 0; sc.Treal = Treal; sc.sph = 0;
+    /* T4's top bit: the scene's triangles come in pairs on one v0 (rt_prep_scene: RT_HDR_PAIRED) */
+    sc.T = T4 & 0x7fffffffu;
+    if (T4 & 0x80000000u) return closest_hit<false, false, 4, true>(sc, o, d, tmin, tmax, dist, id);
     return closest_hit<false, false, 4>(sc, o, d, tmin, tmax, dist, id);
 }
 
@@ -225,9 +228,10 @@ drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, f
     const size_t pix = (size_t)ly * (uint32_t)p.width + x;
 
     const float4 *base = (const float4 *)(sm + lay.isect);
-    const uint32_t T4 = (lay.T + 3u) & ~3u;
+    const uint32_t Tpad = (lay.T + 3u) & ~3u;
+    const uint32_t T4 = Tpad | (((const uint32_t *)sm)[RT_HDR_PAIRED] ? 0x80000000u : 0u);   /* flag for closest_b */
     SceneRef<false> sc;
-    sc.base = base; sc.T = T4; sc.S = 0; sc.Treal = lay.T; sc.sph = 0;
+    sc.base = base; sc.T = Tpad; sc.S = 0; sc.Treal = lay.T; sc.sph = 0;
 
     const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
     const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);

@@ -240,19 +240,29 @@ struct SceneRef {
 /* Both loops run over the PADDED counts T4 = T rounded up to 4 and S4 = S rounded up
  * to 4 (the prepared scene pads with primitives that can never be accepted), so the
  * unrolled bodies need no remainder code: less SASS, same results. */
-template <bool CONST_BANK, bool PRIMARY, int UNROLL>
+template <bool CONST_BANK, bool PRIMARY, int UNROLL, bool PAIRED = false>
 __device__ __forceinline__ bool closest_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3 d, float tmin, float tmax,
                                             float &dist, uint32_t &id) {
+    static_assert(!PAIRED || (UNROLL % 2 == 0 && !PRIMARY), "PAIRED: see any_hit");
     float bestN = tmax, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
 #pragma unroll 1
     for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+        f3 w = mk(0.0f, 0.0f, 0.0f), c = w;
 #pragma unroll
         for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
             float N, a;
-            bool hit = PRIMARY ? tri_test_primary(sc.ld(4 * i + 3), sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), d, tmin, bestN, bestD, N, a)
-                               : tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, bestN, bestD, N, a);
+            bool hit;
+            if (PAIRED) {                              /* second triangle of a pair: same v0, so same w and c */
+                const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+                const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+                if (!(u & 1)) { w = mk(A.x, A.y, A.z) - o; c = cross(d, w); }
+                hit = tri_accept(dot(d, n), dot(w, n), dot(e2, c), dot(e1n, c), tmin, bestN, bestD, N, a);
+            } else {
+                hit = PRIMARY ? tri_test_primary(sc.ld(4 * i + 3), sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), d, tmin, bestN, bestD, N, a)
+                              : tri_test(sc.ld(4 * i), sc.ld(4 * i + 1), sc.ld(4 * i + 2), o, d, tmin, bestN, bestD, N, a);
+            }
             if (hit) { bestN = N; bestD = a; best = i; }
         }
     }
