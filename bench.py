@@ -31,7 +31,14 @@ METRIC = "Mpaths/s, Cornell 1080p x 1024spp at 1/2/4/8 B200; % of FP32 peak"
 UNIT = "Mpaths/s"
 W, H = 1920, 1080
 TILE_ROWS = 8
-NCU_DRAM_BYTES_PER_LAUNCH = 8384000 + 3840      # profiles/r01b_ncu_full_pathTrace_smem_64spp.txt
+def ncu_constants():
+    """Figures taken from the committed `ncu --set full` capture of this kernel (tools/ncu_constants.py writes the
+    file from the .ncu-rep): DRAM bytes of one launch and the FP32 flops the kernel executes per path."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_constants.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
 
 
 def parse():
@@ -257,8 +264,10 @@ def run_ours(a, rank, world, local_rank):
     assert paths == frame_paths, (paths, frame_paths)
     T = scene.num_triangles
     flops = 45 * T * (closest + shadow) + 200 * shaded + 60 * paths          # the contract figure
-    # what the kernel executes: 36 flop per triangle test (precomputed-normal form), 28 for camera rays
-    flops_exec = T * (28 * paths + 36 * (closest - paths + shadow)) + 200 * shaded + 60 * paths
+    # what the kernel EXECUTES (it shares work between the tests of a query and skips camera-ray tests the formula
+    # charges): thread-level FADD + FMUL + 2 FFMA per path from the committed ncu capture, or null without one
+    nc = ncu_constants()
+    flops_exec = nc["executed_fp32_flop_per_path"] * paths if nc and a.width == 1920 and a.height == 1080 and a.bounces == 3 else None
     info = r.device.info()
     k_ms = sum(kernel_ms) / len(kernel_ms)                # this rank's prep+trace per step
     peak = info.smCount * 128 * 2 * (info.clockKHz * 1e3) / 1e12
@@ -272,11 +281,13 @@ def run_ours(a, rank, world, local_rank):
                    "h2d_bytes_per_step": int(h2d_t.item()), "d2h_bytes_per_step": W * H * 16},
            "gpu_launches": launches * world,
            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                        "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
-                        "traffic_note": "dram__bytes_read+write of one pathTrace launch from the ncu --set full capture in "
-                                        "profiles/ (offsets read once; the 33 MB of output is still in L2 when the launch ends)",
-                        "executed_flops_frac": flops_exec * my_share / (k_ms * 1e-3) / 1e12 / peak,
-                        "executed_flops_per_path": flops_exec / paths,
+                        "traffic": nc["dram_bytes_per_launch"] if nc else None,
+                        "traffic_note": "dram__bytes_read+write of one 1080p pathTrace launch from the ncu --set full capture "
+                                        + (nc["source"] if nc else "(none)") +
+                                        " (offsets read once; the 33 MB of output is still in L2 when the launch ends)",
+                        "executed_flops_frac": flops_exec * my_share / (k_ms * 1e-3) / 1e12 / peak if flops_exec else None,
+                        "executed_flops_per_path": flops_exec / paths if flops_exec else None,
+                        "executed_flops_note": "thread-level FADD + FMUL + 2 FFMA of the same ncu capture, per path",
                         "peak_kind": f"nominal {info.smCount} SMs x 128 lanes x 2 x {info.clockKHz / 1e3:.0f} MHz "
                                      "(MEASURED_PEAKS.json has no FP32 figure)",
                         "kernel": "pathTrace (prep + trace), rank 0", "kernel_ms": k_ms,

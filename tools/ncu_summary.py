@@ -35,6 +35,17 @@ for r in rows[2:]:
     for k in WANT:
         if k in d:
             out.append(f"{k:90s} {units[hdr.index(k)]:14s} {d[k]}")
+    # executed FP32 flops: thread-level FADD + FMUL + 2 FFMA, from the per-cycle rates (summed over sub-partitions) x cycles
+    try:
+        f = lambda k: float(d[k].replace(",", ""))
+        rate = (f("smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed") + f("smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed")
+                + 2 * f("smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed"))
+        cycles = f("sm__cycles_elapsed.avg")
+        peak = f("sm__sass_thread_inst_executed_op_ffma_pred_on.sum.peak_sustained") * 2
+        out.append(f"{'executed FP32 flop (FADD + FMUL + 2 FFMA, thread level)':90s} {'flop':14s} {rate * cycles:.6e}")
+        out.append(f"{'executed FP32 flop per cycle / peak (SMs x 128 x 2)':90s} {'':14s} {rate:.1f} / {peak:.0f} = {rate / peak * 100:.2f} %")
+    except (KeyError, ValueError):
+        pass
     stalls = [(float(d[h].replace(",", "") or 0), h) for h in hdr
               if h.startswith("smsp__average_warps_issue_stalled") and h.endswith("_per_issue_active.ratio")]
     out.append("-- warp stall reasons (avg warps stalled per issue-active cycle), top 8")
