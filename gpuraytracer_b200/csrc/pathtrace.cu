@@ -873,10 +873,12 @@ RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 8, 3)
 RT_WAVE_PERSIST_ENTRY(pathTrace_tiles4, false, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4, false)
 RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4, false)
+#ifdef RT_TUNING_VARIANTS   /* queue depth x occupancy sweep (variants 5, 6, 10, 12 of tools/time_variants.py): tools/build_exp.sh */
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp6, false, 4, 6, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
+#endif
 
 #include "modeb.cuh"
 
