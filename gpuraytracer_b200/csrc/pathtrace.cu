@@ -859,23 +859,24 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
         pathtrace_wave_body<COUNT, UNROLL, R, true, false>(scene, offsets, out, p, lay, sm, counters, ts);       \
     }
 /* warp-level path compaction, R samples per pixel per round; rtcuda.cpp adds the queue memory.
- * pathTrace_wave (R = 8) is the default kernel; exp8 / exp10 (R = 4 / 2) are kept for the tuning record
- * (profiles/r01h_variants_wave.txt), like the unroll x occupancy sweep of pathTrace_smem before them
- * (profiles/r01c_variants.txt: all within 2 %). */
-RT_WAVE_ENTRY(pathTrace_wave, false, 4, 8, 3, false)
-RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 8, 3, false)
-/* R = 4: half the queue memory; the library picks it when a large scene leaves room for fewer than
- * three R = 8 blocks per SM (256-sphere scene: 366 -> 482 Mpaths/s) */
+ * R = 6 with four blocks per SM is the default (46 KB of queues per block): measured 5 615 Mpaths/s against
+ * 5 392 for R = 8 with three blocks, 5 482 for R = 5, 4 889 for R = 12 with two (profiles/r02c_variants_R.txt).
+ * Earlier in the kernel's life occupancy did not matter (r01c, r01h); it does since the primitive loops shrank
+ * and the latency-bound code between them became a larger share. */
+RT_WAVE_ENTRY(pathTrace_wave, false, 4, 6, 4, false)
+RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 6, 4, false)
+/* R = 4: two thirds of the queue memory; the library picks it when a large scene leaves room for fewer than
+ * four R = 6 blocks per SM (256-sphere scene) */
 /* fewer samples per launch than a round has slots: G = R / spp tiles side by side per warp (wave.cuh: SPATIAL) */
-RT_WAVE_ENTRY(pathTrace_wide, false, 4, 8, 3, true)
+RT_WAVE_ENTRY(pathTrace_wide, false, 4, 6, 4, true)
 RT_WAVE_ENTRY(pathTrace_wide4, false, 4, 4, 4, true)
-RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 8, 3)
+RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 6, 4)
 RT_WAVE_PERSIST_ENTRY(pathTrace_tiles4, false, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4, false)
 RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4, false)
 #ifdef RT_TUNING_VARIANTS   /* queue depth x occupancy sweep (variants 5, 6, 10, 12 of tools/time_variants.py): tools/build_exp.sh */
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4, false)
-RT_WAVE_ENTRY(pathTrace_exp6, false, 4, 6, 4, false)
+RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 8, 3, false)
 RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
 #endif

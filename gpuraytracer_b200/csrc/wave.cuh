@@ -29,16 +29,17 @@
 #define RT_WAVE_FIELDS 12
 #define RT_WAVE_RES 3
 
-/* Work distribution of the persistent form (pathTrace_tiles): a unit is one 8x4 tile x one CHUNK of
- * chunkSpp consecutive samples; units are handed out chunk-major (every tile's chunk 0, then every tile's
- * chunk 1, ...).  Chunk c of a tile continues the running sum chunk c-1 left in the output buffer -- the
- * same in-order fp32 sum as one pass over all samples -- and waits for flags[tile] == c first; the unit it
- * waits for was handed out a whole image earlier to a warp that is running, so the wait is short and
- * cannot deadlock.  Small units are what keeps every SM busy to the end when a GPU has only a few tiles
- * per warp (1080p over 8 GPUs: 4.6), where whole tiles leave the last round 40 % idle. */
+/* Work distribution of the persistent form (pathTrace_tiles): a unit is one 16x8-pixel block tile x one CHUNK
+ * of chunkSpp consecutive samples; units are handed out chunk-major (every tile's chunk 0, then every tile's
+ * chunk 1, ...) to whole blocks.  Chunk c of a warp's 8x4 pixels continues the running sum chunk c-1 left in
+ * the output buffer -- the same in-order fp32 sum as one pass over all samples -- and waits for
+ * flags[that warp tile] == c first; the unit it waits for was handed out a whole image earlier to a block that
+ * is running, so the wait is short and cannot deadlock.  Small units are what keeps every SM busy to the end
+ * when a GPU has only a few tiles per warp (1080p over 8 GPUs: 4.6), where whole tiles leave the last round
+ * 40 % idle. */
 struct RTTileSched {
     unsigned int *counter;     /* next unit; zeroed by rt_prep_scene (prepared-scene header) */
-    unsigned int *flags;       /* per tile: chunks completed; zeroed by the host before the launch */
+    unsigned int *flags;       /* per warp tile (4 per block tile): chunks completed; zeroed by the host before the launch */
     uint32_t chunks, chunkSpp;
 };
 
@@ -91,7 +92,6 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
      * its next tile from an atomic counter until the image is used up (no block-wide step after the
      * staging above), so an SM is busy until the last tile is handed out; otherwise the tile is the
      * warp's place in the block's 16x8 pixels. */
-    const uint32_t tilesX = ((uint32_t)p.width + 7u) >> 3, tilesY = ((uint32_t)p.rows + 3u) >> 2;
     /* SPATIAL (launches with fewer samples per pixel than the R slots of a round, progressive rendering): the
      * warp takes G = R / spp tiles side by side (sub-tile t = pixels x + 8t) and a round's slot j is sample
      * j % spp of sub-tile j / spp, so the queue is as full as with R samples of one tile.  One round per warp;
@@ -100,14 +100,22 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     for (;;) {
     uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
     if (PERSIST) {
-        uint32_t unit = 0;
-        if (lane == 0) unit = atomicAdd(ts.counter, 1u);
-        unit = __shfl_sync(0xffffffffu, unit, 0);
-        const uint32_t nTiles = tilesX * tilesY;
-        if (unit >= nTiles * ts.chunks) break;
-        chunk = unit / nTiles; tile = unit - chunk * nTiles;
+        /* the BLOCK draws the unit (its four warps stay in step, which keeps them in the same loops and the
+         * instruction cache warm: one unit per warp, each at its own place in the code, measured 4 % slower) */
+        uint32_t *s_unit = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * WaveSmem<R>::WORDS_PER_WARP) +
+                           (RT_BLOCK_THREADS / 32) * (((lay.T + 31u) >> 5) + ((lay.S + 31u) >> 5));
+        __syncthreads();
+        if (threadIdx.x == 0) *s_unit = atomicAdd(ts.counter, 1u);
+        __syncthreads();
+        const uint32_t unit = *s_unit;
+        const uint32_t blocksX = ((uint32_t)p.width + RT_BLOCK_W - 1u) / RT_BLOCK_W, blocksY = ((uint32_t)p.rows + RT_BLOCK_H - 1u) / RT_BLOCK_H;
+        const uint32_t nBlocks = blocksX * blocksY;
+        if (unit >= nBlocks * ts.chunks) break;
+        chunk = unit / nBlocks;
+        const uint32_t bt = unit - chunk * nBlocks;
+        tile = bt * (RT_BLOCK_THREADS / 32) + warp;                    /* this warp's flag: same pixels in every chunk */
         kBegin = chunk * ts.chunkSpp; kEnd = min(p.spp, kBegin + ts.chunkSpp);
-        x0 = (tile % tilesX) * 8u; ly0 = (tile / tilesX) * 4u;
+        x0 = (bt % blocksX) * RT_BLOCK_W + (warp & 1) * 8; ly0 = (bt / blocksX) * RT_BLOCK_H + (warp >> 1) * 4;
     } else {
         x0 = (blockIdx.x * RT_BLOCK_W + (warp & 1) * 8) * G; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
     }
