@@ -849,7 +849,7 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
         extern __shared__ __align__(16) float sm[];                                                              \
         pathtrace_wave_body<COUNT, UNROLL, R, false, SPATIAL>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
     }
-/* persistent form: grid = one resident wave, (tile, sample chunk) units from an atomic counter (wave.cuh: RTTileSched) */
+/* ticketed form: one block per (tile, sample chunk) unit, named by a ticket from an atomic counter (wave.cuh: RTTileSched) */
 #define RT_WAVE_PERSIST_ENTRY(name, COUNT, UNROLL, R, MINB)                                                      \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \

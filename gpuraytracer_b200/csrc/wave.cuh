@@ -29,19 +29,36 @@
 #define RT_WAVE_FIELDS 12
 #define RT_WAVE_RES 3
 
-/* Work distribution of the persistent form (pathTrace_tiles): a unit is one 16x8-pixel block tile x one CHUNK
- * of chunkSpp consecutive samples; units are handed out chunk-major (every tile's chunk 0, then every tile's
- * chunk 1, ...) to whole blocks.  Chunk c of a warp's 8x4 pixels continues the running sum chunk c-1 left in
- * the output buffer -- the same in-order fp32 sum as one pass over all samples -- and waits for
- * flags[that warp tile] == c first; the unit it waits for was handed out a whole image earlier to a block that
- * is running, so the wait is short and cannot deadlock.  Small units are what keeps every SM busy to the end
- * when a GPU has only a few tiles per warp (1080p over 8 GPUs: 4.6), where whole tiles leave the last round
- * 40 % idle. */
+/* Work distribution of pathTrace_tiles: a unit is one 16x8-pixel block tile x one CHUNK of chunkSpp consecutive
+ * samples, one unit per block, the grid is tiles x chunks blocks.  A block takes a ticket from an atomic counter
+ * and the ticket, not blockIdx, names its unit, chunk-major (every tile's chunk 0, then every tile's chunk 1, ...),
+ * so units start in that order.  Chunk c of a warp's 8x4 pixels continues the running sum chunk c-1 left in the
+ * output buffer -- the same in-order fp32 sum as one pass over all samples -- and waits for
+ * flags[that warp tile] == c first; the unit it waits for started a whole image earlier and is running or done,
+ * so the wait is short and cannot deadlock.  Small units are what keeps every SM busy to the end when a GPU has
+ * only a few blocks per SM (1080p over 8 GPUs: 3.4 waves), where whole tiles leave the last wave half idle.
+ * (Tried first: a persistent grid whose warps, then blocks, loop over units -- same loops, 5 % slower.) */
 struct RTTileSched {
     unsigned int *counter;     /* next unit; zeroed by rt_prep_scene (prepared-scene header) */
     unsigned int *flags;       /* per warp tile (4 per block tile): chunks completed; zeroed by the host before the launch */
     uint32_t chunks, chunkSpp;
 };
+
+/* the two rare steps of a chunked unit, out of line so that they do not disturb the register allocation of the loops */
+__device__ __noinline__ float4 tiles_wait_for_previous_chunk(const unsigned int *flag, uint32_t chunk, const float4 *src, bool owns) {
+    if ((threadIdx.x & 31) == 0) {
+        unsigned int done;
+        do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(flag) : "memory"); } while (done < chunk);
+    }
+    __syncwarp();
+    return owns ? __ldcg(src) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+__device__ __noinline__ void tiles_publish_chunk(unsigned int *flag, uint32_t chunk, float4 *dst, float4 sum, bool owns) {
+    if (owns) __stcg(dst, sum);
+    __threadfence();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(flag), "r"(chunk + 1u) : "memory");
+}
 
 template <int R>
 struct WaveSmem {
@@ -88,10 +105,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     Counters cnt = { 0u, 0u, 0u };
     unsigned long long paths = 0ull;
 
-    /* One 8x4-pixel tile per warp.  PERSIST: the grid is one resident wave of blocks and every WARP draws
-     * its next tile from an atomic counter until the image is used up (no block-wide step after the
-     * staging above), so an SM is busy until the last tile is handed out; otherwise the tile is the
-     * warp's place in the block's 16x8 pixels. */
+    /* One 8x4-pixel tile per warp: its place in the block's 16x8 pixels; PERSIST: the block's unit comes from a ticket. */
     /* SPATIAL (launches with fewer samples per pixel than the R slots of a round, progressive rendering): the
      * warp takes G = R / spp tiles side by side (sub-tile t = pixels x + 8t) and a round's slot j is sample
      * j % spp of sub-tile j / spp, so the queue is as full as with R samples of one tile.  One round per warp;
@@ -100,8 +114,8 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     for (;;) {
     uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
     if (PERSIST) {
-        /* the BLOCK draws the unit (its four warps stay in step, which keeps them in the same loops and the
-         * instruction cache warm: one unit per warp, each at its own place in the code, measured 4 % slower) */
+        /* the block draws its unit from the counter instead of reading blockIdx: units START in unit order whatever
+         * order the hardware dispatches blocks in, which is what makes waiting for the previous chunk safe */
         uint32_t *s_unit = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * WaveSmem<R>::WORDS_PER_WARP) +
                            (RT_BLOCK_THREADS / 32) * (((lay.T + 31u) >> 5) + ((lay.S + 31u) >> 5));
         __syncthreads();
@@ -145,13 +159,9 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     const uint32_t offset = owns ? offsets[pix] : 0u;
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (PERSIST && chunk > 0) {
-        /* the running sum of the samples before kBegin, once the warp that made it has published it */
-        if (lane == 0) {
-            unsigned int done;
-            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(ts.flags + tile) : "memory"); } while (done < chunk);
-        }
-        __syncwarp();
-        if (owns) { float4 o = __ldcg(out + pix); lum = mk(o.x, o.y, o.z); }
+        /* the running sum of the samples before kBegin, once the block that made it has published it */
+        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
+        lum = mk(o.x, o.y, o.z);
     } else if (!SPATIAL && p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 
 #pragma unroll 1
@@ -381,10 +391,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
         /* stored per sub-tile above */
     } else if (PERSIST && kEnd < p.spp) {
         /* not the last chunk: leave the running sum for the next one and publish it */
-        if (owns) __stcg(out + pix, make_float4(lum.x, lum.y, lum.z, 0.0f));
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(ts.flags + tile), "r"(chunk + 1u) : "memory");
+        tiles_publish_chunk(ts.flags + tile, chunk, out + pix, make_float4(lum.x, lum.y, lum.z, 0.0f), owns);
     } else if (owns) {
         float4 o;
         if (p.accumulate) {
@@ -396,7 +403,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
         out[pix] = o;
     }
     if (COUNT && owns && !SPATIAL) paths += kEnd - kBegin;
-    if (!PERSIST) break;
+    break;           /* one unit per block: the grid is blocks x chunks (a persistent loop here was measured 5 % slower) */
     }
 #undef QF
 #undef QU

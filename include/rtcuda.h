@@ -76,8 +76,8 @@ enum {
 enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
 /* kernel variants of pathTrace (all give bit-identical images): DEFAULT picks WAVE, or SMEM when a launch
  * has fewer than 4 samples per pixel; SMEM = one thread walks one pixel's samples; CONST = the same with the
- * primitives in the constant bank; WAVE = warp-level path compaction (csrc/wave.cuh); TILES = WAVE as a
- * persistent grid drawing (tile, sample chunk) units from a counter, picked by DEFAULT for launches with few
+ * primitives in the constant bank; WAVE = warp-level path compaction (csrc/wave.cuh); TILES = WAVE with one
+ * block per (tile, sample chunk) unit, named by a ticket from a counter, picked by DEFAULT for launches with few
  * blocks per SM (one rank's share of a multi-GPU frame); WIDE = WAVE for launches with fewer than 6 samples per
  * pixel (progressive rendering): a warp takes 6 / spp tiles side by side so that its path queue is as full */
 enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17,
