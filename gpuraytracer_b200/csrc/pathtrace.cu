@@ -34,6 +34,99 @@ __constant__ float4 c_scene[RT_CONST_SLOTS];
 /* ------------------------------------------------------------------ prep ---- */
 struct SimdF3 { float x, y, z, pad; };
 
+/*
+ * Object groups for the sorted kernel (sorted.cuh; layout: rt_scene_layout.h "group").  One warp, lane = quad
+ * (triangles 2*lane, 2*lane+1).  Two quads are connected when some vertex of one is bit-equal to some vertex of
+ * the other; a group is a connected component (the Cornell scene: the room, the tall box, the short box, the
+ * light).  A group whose bounds span 90 % of the scene on every axis is "always tested"; up to RT_MAX_GROUPS
+ * others get a box (bounds of the vertices grown by 1/128 of the scene's largest extent) and a sort-key bit;
+ * what is left over is always tested too.  ANY partition gives the same image -- a group only says which quads
+ * a ray that misses its box may skip -- so nothing here is part of the arithmetic contract.
+ */
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int s = 16; s; s >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, s));
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int s = 16; s; s >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, s));
+    return v;
+}
+__device__ void prep_groups(const unsigned char *__restrict__ vertices, float *__restrict__ scene, const RTSceneLayout lay,
+                            bool paired, uint32_t lane) {
+    uint32_t *gu = (uint32_t *)scene + lay.group;
+    float *gf = scene + lay.group;
+    for (uint32_t k = lane; k < RT_GROUP_WORDS; k += 32u) gu[k] = 0u;
+    __syncwarp();
+    const uint32_t P = lay.T / 2u;
+    if (!(paired && lay.T >= 2u && lay.T <= 64u && lay.S == 0u)) return;          /* warp-uniform */
+    const bool has = lane < P;
+    const float INF = __int_as_float(0x7f800000);
+    uint32_t vb[18];
+    float lo[3] = { INF, INF, INF }, hi[3] = { -INF, -INF, -INF };
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            vb[3 * a + k] = has ? ((const uint32_t *)vertices)[(6u * lane + a) * 4u + k] : 0u;
+            if (has) { const float x = __uint_as_float(vb[3 * a + k]); lo[k] = fminf(lo[k], x); hi[k] = fmaxf(hi[k], x); }
+        }
+    uint32_t adj = 0u;
+    for (uint32_t q = 0; q < P; q++) {
+        bool share = false;
+#pragma unroll
+        for (int b = 0; b < 6; b++) {
+            const uint32_t x = __shfl_sync(0xffffffffu, vb[3 * b], q), y = __shfl_sync(0xffffffffu, vb[3 * b + 1], q),
+                           z = __shfl_sync(0xffffffffu, vb[3 * b + 2], q);
+#pragma unroll
+            for (int a = 0; a < 6; a++) share |= vb[3 * a] == x && vb[3 * a + 1] == y && vb[3 * a + 2] == z;
+        }
+        if (share && has) adj |= 1u << q;
+    }
+    uint32_t label = lane;
+    for (uint32_t it = 0; it < P; it++) {
+        uint32_t best = label;
+        for (uint32_t q = 0; q < P; q++) {
+            const uint32_t l = __shfl_sync(0xffffffffu, label, q);
+            if ((adj >> q) & 1u) best = min(best, l);
+        }
+        const bool changed = best != label;
+        label = best;
+        if (!__any_sync(0xffffffffu, changed)) break;
+    }
+    const uint32_t leaders = __ballot_sync(0xffffffffu, has && label == lane);
+    const uint32_t comp = __popc(leaders & ((1u << label) - 1u)), ncomp = __popc(leaders);
+    float slo[3], shi[3], ext = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; k++) { slo[k] = warp_min(lo[k]); shi[k] = warp_max(hi[k]); ext = fmaxf(ext, shi[k] - slo[k]); }
+    const float margin = ext * (1.0f / 128.0f);
+    uint32_t K = 0u, always = 0u;
+    for (uint32_t c = 0; c < ncomp; c++) {
+        const bool member = has && comp == c;
+        const uint32_t pairs = __ballot_sync(0xffffffffu, member);
+        float glo[3], ghi[3];
+        bool spans = true;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            glo[k] = warp_min(member ? lo[k] : INF); ghi[k] = warp_max(member ? hi[k] : -INF);
+            spans = spans && (ghi[k] - glo[k] >= 0.9f * (shi[k] - slo[k]));
+        }
+        if (!spans && K < RT_MAX_GROUPS) {
+            if (lane == 0) {
+                float *r = gf + 4 + 8 * K;
+#pragma unroll
+                for (int k = 0; k < 3; k++) { r[k] = (glo[k] + ghi[k]) * 0.5f; r[4 + k] = (ghi[k] - glo[k]) * 0.5f + margin; }
+                ((uint32_t *)r)[3] = pairs; r[7] = 0.0f;
+            }
+            K++;
+        } else {
+            always |= pairs;
+        }
+    }
+    if (lane == 0) { gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; }
+}
+
 extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camera,
                                          const unsigned char *__restrict__ materials,
                                          const unsigned char *__restrict__ lights,
@@ -138,6 +231,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         }
         ok = __syncthreads_and(ok);
         if (tid == 0) ((uint32_t *)scene)[RT_HDR_PAIRED] = ok ? 1u : 0u;
+        if (tid < 32) prep_groups(vertices, scene, lay, ok != 0, (uint32_t)tid);
     }
     for (uint32_t l = tid; l < lay.L; l += nth) {
         const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
@@ -882,6 +976,34 @@ RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 8, 3, false)
 RT_WAVE_ENTRY(pathTrace_exp5, false, 4, 5, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
 #endif
+
+#include "sorted.cuh"
+/* rays sorted by the object groups they can reach (sorted.cuh); a block that finds the scene ungrouped
+ * (rt_prep_scene: RT_GRP_OK clear) runs the compacting kernel with R = 4 in the same shared memory */
+#define RT_SORTED_ENTRY(name, R, MINB)                                                                           \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
+            pathtrace_sorted_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{});                     \
+        else                                                                                                     \
+            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
+    }
+#define RT_SORTED_PERSIST_ENTRY(name, R, MINB)                                                                   \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTTileSched ts) {                                                                                 \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
+            pathtrace_sorted_body<R, true>(scene, offsets, out, p, lay, sm, ts);                                 \
+        else                                                                                                     \
+            pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);        \
+    }
+RT_SORTED_ENTRY(pathTrace_sorted4, 4, 4)
+RT_SORTED_ENTRY(pathTrace_sorted6, 6, 3)
+RT_SORTED_ENTRY(pathTrace_sorted8, 8, 2)
 
 #include "modeb.cuh"
 

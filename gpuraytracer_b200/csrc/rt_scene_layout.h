@@ -21,6 +21,13 @@
  *            so SoA keeps different ids on different banks
  *   sshade : RT_SSHADE_ROWS rows of Sp words
  *   light  : 16 words per light     center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0
+ *   group  : RT_GROUP_WORDS words: object groups for the sorted kernel (sorted.cuh), built by rt_prep_scene
+ *            when every triangle 2k+1 shares v0 with 2k (pairs), T <= 64 and S == 0:
+ *            [0] K = number of cullable groups (0..4)   [1] pair mask that is always tested
+ *            [2] 1 when the sorted kernel applies       [3] -
+ *            then K records of 8 words: box centre xyz, pair mask (uint) | inflated half extent xyz, -
+ *            A group is a connected set of quads (connected = some vertex bit-equal), its box the bounds of
+ *            its vertices grown by 1/128 of the scene's largest extent.
  */
 #ifndef RT_SCENE_LAYOUT_H
 #define RT_SCENE_LAYOUT_H
@@ -63,6 +70,11 @@
 #define RT_SSHADE_ROWS    7
 
 #define RT_LIGHT_WORDS   16   /* center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0 */
+#define RT_MAX_GROUPS     4   /* cullable object groups (16 sort keys)                                 */
+#define RT_GROUP_WORDS   (4 + 8 * RT_MAX_GROUPS)
+#define RT_GRP_K          0
+#define RT_GRP_ALWAYS     1
+#define RT_GRP_OK         2
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
 #define RT_CONST_SLOTS   3584
@@ -76,6 +88,7 @@ typedef struct RTSceneLayout {
     uint32_t isect, sphere;                         /* intersection part, section starts in words */
     uint32_t shade, sshade, light;                  /* shading part                               */
     uint32_t words;           /* total size                                          */
+    uint32_t group;           /* object groups (sorted.cuh), RT_GROUP_WORDS words    */
 } RTSceneLayout;
 
 #if defined(__CUDACC__)
@@ -94,7 +107,8 @@ RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
     l.shade   = l.sphere + RT_SPHERE_WORDS * l.Sp;
     l.sshade  = l.shade + RT_SHADE_ROWS * l.Tp;
     l.light   = l.sshade + RT_SSHADE_ROWS * l.Sp;
-    l.words  = l.light + RT_LIGHT_WORDS * L;
+    l.group   = l.light + RT_LIGHT_WORDS * L;
+    l.words  = l.group + RT_GROUP_WORDS;
     l.words  = (l.words + 3u) & ~3u;
     return l;
 }
