@@ -38,7 +38,8 @@ struct SimdF3 { float x, y, z, pad; };
  * Object groups for the sorted kernel (sorted.cuh; layout: rt_scene_layout.h "group").  One warp, lane = quad
  * (triangles 2*lane, 2*lane+1).  Two quads are connected when some vertex of one is bit-equal to some vertex of
  * the other; a group is a connected component (the Cornell scene: the room, the tall box, the short box, the
- * light).  A group whose bounds span 90 % of the scene on every axis is "always tested"; up to RT_MAX_GROUPS
+ * light).  A group whose bounds span 90 % of the scene on every axis, or hold a light's centre (every shadow
+ * ray goes there), is "always tested"; up to RT_MAX_GROUPS
  * others get a box (bounds of the vertices grown by 1/128 of the scene's largest extent) and a sort-key bit;
  * what is left over is always tested too.  ANY partition gives the same image -- a group only says which quads
  * a ray that misses its box may skip -- so nothing here is part of the arithmetic contract.
@@ -53,8 +54,8 @@ __device__ __forceinline__ float warp_max(float v) {
     for (int s = 16; s; s >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, s));
     return v;
 }
-__device__ void prep_groups(const unsigned char *__restrict__ vertices, float *__restrict__ scene, const RTSceneLayout lay,
-                            bool paired, uint32_t lane) {
+__device__ void prep_groups(const unsigned char *__restrict__ vertices, const unsigned char *__restrict__ lights,
+                            float *__restrict__ scene, const RTSceneLayout lay, bool paired, uint32_t lane) {
     uint32_t *gu = (uint32_t *)scene + lay.group;
     float *gf = scene + lay.group;
     for (uint32_t k = lane; k < RT_GROUP_WORDS; k += 32u) gu[k] = 0u;
@@ -112,7 +113,16 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, float *_
             glo[k] = warp_min(member ? lo[k] : INF); ghi[k] = warp_max(member ? hi[k] : -INF);
             spans = spans && (ghi[k] - glo[k] >= 0.9f * (shi[k] - slo[k]));
         }
-        if (!spans && K < RT_MAX_GROUPS) {
+        /* a group that holds a light's centre is reached by every shadow ray: a key bit would always be set */
+        bool lit = false;
+        for (uint32_t l = 0; l < lay.L; l++) {
+            const float *c = (const float *)(lights + 64 * (size_t)l);
+            bool in = true;
+#pragma unroll
+            for (int k = 0; k < 3; k++) in = in && c[k] >= glo[k] - margin && c[k] <= ghi[k] + margin;
+            lit = lit || in;
+        }
+        if (!spans && !lit && K < RT_MAX_GROUPS) {
             if (lane == 0) {
                 float *r = gf + 4 + 8 * K;
 #pragma unroll
@@ -231,7 +241,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         }
         ok = __syncthreads_and(ok);
         if (tid == 0) ((uint32_t *)scene)[RT_HDR_PAIRED] = ok ? 1u : 0u;
-        if (tid < 32) prep_groups(vertices, scene, lay, ok != 0, (uint32_t)tid);
+        if (tid < 32) prep_groups(vertices, lights, scene, lay, ok != 0, (uint32_t)tid);
     }
     for (uint32_t l = tid; l < lay.L; l += nth) {
         const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
@@ -754,20 +764,29 @@ __device__ __forceinline__ void camera_candidates(const SceneRef<false> &sc, con
 /* sampling.metal:198-236 with the literals of :207-209 folded:
  * samplePosition = center + (0.25,0,0)*ux + (0,0,0.25)*uy.  The products with the
  * zero components are +-0 and drop out exactly, so only x and z move. */
-__device__ __forceinline__ f3 sample_area_light(f3 center, f3 lcolor, float ux, float uy, f3 P,
-                                                f3 &ldir, float &ldist) {
+/* the three steps of sampleAreaLight, separately callable (sorted.cuh keeps the sample point and repeats steps
+ * 2 and 3 when it traces): the same operations in the same order as the one-piece form below */
+__device__ __forceinline__ f3 light_sample_point(f3 center, float ux, float uy) {
     ux = ux * 2.0f - 1.0f;
     uy = uy * 2.0f - 1.0f;
-    f3 samplePosition = mk(center.x + 0.25f * ux, center.y, center.z + 0.25f * uy);
+    return mk(center.x + 0.25f * ux, center.y, center.z + 0.25f * uy);
+}
+__device__ __forceinline__ void light_direction(f3 samplePosition, f3 P, f3 &ldir, float &ldist, float &inv) {
     f3 ld = samplePosition - P;
     float dist = length(ld);
-    float inv = 1.0f / fmaxf(dist, 1e-3f);
-    ld = ld * inv;
+    inv = 1.0f / fmaxf(dist, 1e-3f);
+    ldir = ld * inv; ldist = dist;
+}
+__device__ __forceinline__ f3 light_colour(f3 lcolor, float inv, f3 ldir) {
     f3 c = lcolor * (inv * inv);
     /* dot(-ld, (0,-1,0)) = fma(-z,0, fma(-y,-1, -x*0)) = ld.y (the zero terms are exact) */
-    c = c * saturate(ld.y);
-    ldir = ld; ldist = dist;
-    return c;
+    return c * saturate(ldir.y);
+}
+__device__ __forceinline__ f3 sample_area_light(f3 center, f3 lcolor, float ux, float uy, f3 P,
+                                                f3 &ldir, float &ldist) {
+    float inv;
+    light_direction(light_sample_point(center, ux, uy), P, ldir, ldist, inv);
+    return light_colour(lcolor, inv, ldir);
 }
 
 /* sampling.metal:39-49 */
@@ -1001,9 +1020,11 @@ RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
         else                                                                                                     \
             pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);        \
     }
+/* 15 words per slot: R = 6 fits four blocks per SM beside the Cornell scene (53 KB per block) */
 RT_SORTED_ENTRY(pathTrace_sorted4, 4, 4)
-RT_SORTED_ENTRY(pathTrace_sorted6, 6, 3)
-RT_SORTED_ENTRY(pathTrace_sorted8, 8, 2)
+RT_SORTED_ENTRY(pathTrace_sorted5, 5, 4)
+RT_SORTED_ENTRY(pathTrace_sorted6, 6, 4)
+RT_SORTED_ENTRY(pathTrace_sorted8, 8, 3)
 
 #include "modeb.cuh"
 

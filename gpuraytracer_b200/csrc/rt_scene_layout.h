@@ -17,7 +17,7 @@
  *            m = camera.position - center, C = dot(m,m) - r*r (camera rays)
  *   --- shading part ---
  *   shade  : RT_SHADE_ROWS rows of Tp words (structure of arrays, Tp = T rounded
- *            up to 32): looked up with the per-lane primitive id after a hit,
+ *            up to 4): looked up with the per-lane primitive id after a hit,
  *            so SoA keeps different ids on different banks
  *   sshade : RT_SSHADE_ROWS rows of Sp words
  *   light  : 16 words per light     center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0
@@ -84,7 +84,7 @@
 
 typedef struct RTSceneLayout {
     uint32_t T, S, L;
-    uint32_t Tp, Sp;          /* padded to a multiple of 32                          */
+    uint32_t Tp, Sp;          /* padded to a multiple of 4 (the unrolled loops' step) */
     uint32_t isect, sphere;                         /* intersection part, section starts in words */
     uint32_t shade, sshade, light;                  /* shading part                               */
     uint32_t words;           /* total size                                          */
@@ -100,8 +100,8 @@ typedef struct RTSceneLayout {
 RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
     RTSceneLayout l;
     l.T = T; l.S = S; l.L = L;
-    l.Tp = (T + 31u) & ~31u;
-    l.Sp = (S + 31u) & ~31u;
+    l.Tp = (T + 3u) & ~3u;
+    l.Sp = (S + 3u) & ~3u;
     l.isect   = RT_HDR_WORDS;
     l.sphere  = l.isect + RT_ISECT_WORDS * l.Tp;
     l.shade   = l.sphere + RT_SPHERE_WORDS * l.Sp;

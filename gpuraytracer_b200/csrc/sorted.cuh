@@ -37,14 +37,14 @@
  */
 #pragma once
 
-#define RT_SORT_FIELDS 16      /* X.xyz D.xyz colour.xyz LD.xyz ltmax LC.xyz */
+#define RT_SORT_FIELDS 11      /* X.xyz (hit point, then P)  D.xyz (continuation ray)  colour.xyz  light sample point x, z */
 #define RT_SORT_KEYS   (1 << RT_MAX_GROUPS)
 
 template <int R>
 struct SortSmem {
     static constexpr uint32_t CAP = 32u * R;                      /* slots per warp = paths per round; one byte names a slot */
     static_assert(CAP <= 256u, "slot numbers are bytes");
-    /* fields + res.xyz + four byte lists (hit list, hit ids, sorted list, keys) + the lanes' offsets + key counters */
+    /* fields + res.xyz + four byte lists (hit list, sorted list; surface id and key per slot) + the lanes' offsets + key counters */
     static constexpr uint32_t WORDS_PER_WARP = (RT_SORT_FIELDS + 3u + 1u) * CAP + 32u + RT_SORT_KEYS;
 };
 
@@ -148,7 +148,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
     /* this warp's slots, lists and counters, after the scene */
     float *Q = sm + lay.words + warp * SortSmem<R>::WORDS_PER_WARP;
     float *res = Q + RT_SORT_FIELDS * CAP;
-    uint8_t *hitlist = (uint8_t *)(res + 3 * CAP), *hitid = hitlist + CAP, *sorted = hitid + CAP, *keyarr = sorted + CAP;
+    uint8_t *hitlist = (uint8_t *)(res + 3 * CAP), *idarr = hitlist + CAP, *sorted = idarr + CAP, *keyarr = sorted + CAP;
     uint32_t *offs = (uint32_t *)(keyarr + CAP);
     uint32_t *cnts = offs + 32;
 #define SF(field, s) Q[(field) * CAP + (s)]
@@ -166,12 +166,20 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const uint32_t nb = (uint32_t)p.bounces;
     const uint32_t *grp = (const uint32_t *)(sm + lay.group);
-    const uint32_t K = grp[RT_GRP_K], alwaysPairs = grp[RT_GRP_ALWAYS];
+    const uint32_t K = grp[RT_GRP_K];
+    const uint32_t mwT = (lay.T + 31u) >> 5;
+    uint32_t *tail = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * SortSmem<R>::WORDS_PER_WARP);
+    /* the quads each key names: always-tested ones + those of the groups whose bit is set */
+    uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1;
+    if (threadIdx.x < RT_SORT_KEYS) {
+        uint32_t pm = grp[RT_GRP_ALWAYS];
+        for (uint32_t g = 0; g < K; g++) if ((threadIdx.x >> g) & 1u) pm |= grp[4 + 8 * g + 3];
+        keyPairs[threadIdx.x] = pm;
+    }
+    __syncthreads();
 
     for (;;) {
     uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
-    uint32_t *tail = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * SortSmem<R>::WORDS_PER_WARP);
-    const uint32_t mwT = (lay.T + 31u) >> 5;
     if (PERSIST) {
         /* the block's unit comes from a ticket (wave.cuh: RTTileSched) */
         uint32_t *s_unit = tail + (RT_BLOCK_THREADS / 32) * mwT;
@@ -263,7 +271,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     const uint32_t e = count + __popc(mask & lt);
                     SF(0, slot) = hp[q].x; SF(1, slot) = hp[q].y; SF(2, slot) = hp[q].z;
                     SF(6, slot) = 1.0f; SF(7, slot) = 1.0f; SF(8, slot) = 1.0f;
-                    hitlist[e] = (uint8_t)slot; hitid[e] = (uint8_t)id[q];
+                    hitlist[e] = (uint8_t)slot; idarr[slot] = (uint8_t)id[q];
                 }
                 res[0 * CAP + slot] = r0[q].x; res[1 * CAP + slot] = r0[q].y; res[2 * CAP + slot] = r0[q].z;
                 count += __popc(mask);
@@ -284,7 +292,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 const bool active = e < count;
                 uint32_t key = 0xffu;
                 if (active) {
-                    const uint32_t slot = hitlist[e], id = hitid[e];
+                    const uint32_t slot = hitlist[e], id = idarr[slot];
                     const uint32_t i = offs[slot & 31u] + (ibase + (slot >> 5));
                     const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
                     f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
@@ -303,10 +311,9 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
                     }
                     const float *L = sm + lay.light;
-                    f3 ldir; float ldist;
-                    f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
-                    lightColor = lightColor * saturate(dot(normal, ldir));                      /* :75 */
-                    const f3 lc = lightColor * color;                                           /* the product of :88 */
+                    const f3 sp = light_sample_point(mk(L[0], L[1], L[2]), wx, wy);             /* sampling.metal:207-212 */
+                    f3 ldir; float ldist, inv;
+                    light_direction(sp, P, ldir, ldist, inv);                                   /* repeated in B, bit for bit */
                     /* which groups can the two rays reach? */
                     key = 0u;
                     for (uint32_t g = 0; g < K; g++) {
@@ -317,11 +324,9 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                         if (!clear) key |= 1u << g;
                     }
                     SF(0, slot) = P.x; SF(1, slot) = P.y; SF(2, slot) = P.z;
-                    SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z;
+                    if (cont) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
                     SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
-                    SF(9, slot) = ldir.x; SF(10, slot) = ldir.y; SF(11, slot) = ldir.z;
-                    SF(12, slot) = ldist - 1e-3f;
-                    SF(13, slot) = lc.x; SF(14, slot) = lc.y; SF(15, slot) = lc.z;
+                    SF(9, slot) = sp.x; SF(10, slot) = sp.z;
                     keyarr[slot] = (uint8_t)key;
                 }
                 if (sort) {
@@ -374,15 +379,16 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 const uint32_t slot = active ? order[e] : 0u;
                 const uint32_t key = active ? keyarr[slot] : 0u;
                 __syncwarp();                                                  /* the chunk's entries are read: the hit list may be rewritten */
-                const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
-                uint32_t pairs = alwaysPairs;
-                for (uint32_t g = 0; g < K; g++) if ((keys >> g) & 1u) pairs |= grp[4 + 8 * g + 3];
+                const uint32_t pairs = keyPairs[__reduce_or_sync(0xffffffffu, key)];
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {
                     const f3 P = mk(SF(0, slot), SF(1, slot), SF(2, slot));
-                    const f3 ldir = mk(SF(9, slot), SF(10, slot), SF(11, slot));
-                    const float ltmax = SF(12, slot);
+                    const float *L = sm + lay.light;
+                    f3 ldir; float ldist, inv;
+                    light_direction(mk(SF(9, slot), L[1], SF(10, slot)), P, ldir, ldist, inv);  /* sampling.metal:214-220 */
+                    const float ltmax = ldist - 1e-3f;                                          /* raytrace.metal:81 */
+                    const uint32_t surf = idarr[slot];
                     bool shadowed, hitC = false;
                     float dist = 0.0f;
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
@@ -392,10 +398,15 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     } else {
                         shadowed = any_hit_pairs(sc, pairs, P, ldir, 0.0f, ltmax);
                     }
-                    if (!shadowed) {                                                            /* :88 */
-                        res[0 * CAP + slot] = res[0 * CAP + slot] + SF(13, slot);
-                        res[1 * CAP + slot] = res[1 * CAP + slot] + SF(14, slot);
-                        res[2 * CAP + slot] = res[2 * CAP + slot] + SF(15, slot);
+                    if (!shadowed) {                                                            /* :74-75, :88 */
+                        const float *sh = sm + lay.shade + surf;
+                        const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                        f3 lightColor = light_colour(mk(L[4], L[5], L[6]), inv, ldir);
+                        lightColor = lightColor * saturate(dot(normal, ldir));
+                        const f3 lc = lightColor * mk(SF(6, slot), SF(7, slot), SF(8, slot));
+                        res[0 * CAP + slot] = res[0 * CAP + slot] + lc.x;
+                        res[1 * CAP + slot] = res[1 * CAP + slot] + lc.y;
+                        res[2 * CAP + slot] = res[2 * CAP + slot] + lc.z;
                     }
                     if (hitC) {
                         const float *sh = sm + lay.shade + id;
@@ -412,7 +423,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 const uint32_t mask = __ballot_sync(0xffffffffu, alive);
                 if (alive) {
                     const uint32_t o = m + __popc(mask & lt);
-                    hitlist[o] = (uint8_t)slot; hitid[o] = (uint8_t)id;
+                    hitlist[o] = (uint8_t)slot; idarr[slot] = (uint8_t)id;
                 }
                 m += __popc(mask);
                 __syncwarp();
