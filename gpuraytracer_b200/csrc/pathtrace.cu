@@ -1025,6 +1025,8 @@ RT_SORTED_ENTRY(pathTrace_sorted4, 4, 4)
 RT_SORTED_ENTRY(pathTrace_sorted5, 5, 4)
 RT_SORTED_ENTRY(pathTrace_sorted6, 6, 4)
 RT_SORTED_ENTRY(pathTrace_sorted8, 8, 3)
+/* ticketed (tile, sample chunk) units for launches with few blocks per SM (wave.cuh: RTTileSched) */
+RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
 
 #include "modeb.cuh"
 
@@ -1056,7 +1058,8 @@ extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar
  *       1 sincos(x)   [in: float]              -> float2
  *       2 hash(x)     [in: u32]                -> u32
  *       3 halton_rt(i,d)                       -> float  (generic loop)
- *       4 halton_slot<s>(i,b), in: (i, 4*b+s)  -> float  (the path tracer's table-driven form) */
+ *       4 halton_slot<s>(i,b), in: (i, 4*b+s)  -> float  (the path tracer's table-driven form)
+ *       5 one triangle test; 6 rt_prep_scene's object groups of a scene (see below) */
 template <int D>
 __device__ float halton_dispatch(uint32_t i, uint32_t d) {
     if (d == D) return halton<D>(i);
@@ -1065,6 +1068,18 @@ __device__ float halton_dispatch(uint32_t i, uint32_t d) {
 
 extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, void *__restrict__ out, uint32_t n) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (what == 6) {
+        /* the object groups rt_prep_scene makes of a scene: in = T, L, paired, - (uint32), then 48*T bytes of
+         * vertices, then 64*L bytes of lights; out = the RT_GROUP_WORDS words of the "group" section */
+        if (k < 32) {
+            const uint32_t *h = (const uint32_t *)in;
+            RTSceneLayout lay = rtSceneLayout(h[0], 0u, h[1]);
+            lay.group = 0u;
+            const unsigned char *v = (const unsigned char *)in + 16;
+            prep_groups(v, v + 48 * (size_t)h[0], (float *)out, lay, h[2] != 0u, k);
+        }
+        return;
+    }
     if (k >= n) return;
     if (what == 0) {
         const uint32_t *p = (const uint32_t *)in;

@@ -1,0 +1,176 @@
+/*
+ * rt_groups.c -- TEST INFRASTRUCTURE.  CPU restatement of what the sorted kernel adds to the path
+ * (gpuraytracer_b200/csrc/pathtrace.cu: prep_groups; csrc/sorted.cuh: ray_clear_of_box), and the check that it
+ * cannot change a result:
+ *
+ *   rt_oracle_groups      the object groups of a scene, word for word the "group" section of the prepared scene
+ *                         (rt_scene_layout.h): quads (triangles 2k, 2k+1 on one v0) are connected when they have a
+ *                         bit-equal vertex; a group = a connected component; a group that spans 90 % of the scene
+ *                         on every axis or holds a light's centre is always tested; up to 4 others get a box
+ *                         (bounds grown by 1/128 of the scene's largest extent) and a key bit
+ *   rt_oracle_cullcheck   traces a frame with the oracle and, for EVERY ray query of it, repeats the query against
+ *                         only the quads of the groups whose box the ray does not stay clear of: hit / miss,
+ *                         primitive id and distance must be the full query's, bit for bit.  Also counts the keys.
+ *
+ * The reference has no counterpart (its queries go to Metal's acceleration structure); nothing here is part of
+ * the arithmetic contract -- a group only says which quads a ray may skip.
+ */
+#include "rt_oracle.h"
+#include "rt_detmath.h"
+#include <string.h>
+
+#define RT_MAX_GROUPS 4
+#define RT_GROUP_WORDS (4 + 8 * RT_MAX_GROUPS)
+
+extern void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
+                                    int hit, float distance, uint32_t primitive_id);
+
+int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L,
+                     uint32_t out[RT_GROUP_WORDS]) {
+    const float *v = (const float *)vertices;
+    memset(out, 0, 4 * RT_GROUP_WORDS);
+    int paired = T >= 2 && T % 2 == 0;
+    for (uint32_t i = 1; i < T && paired; i += 2)
+        if (memcmp(v + (size_t)(i - 1) * 12, v + (size_t)i * 12, 12)) paired = 0;
+    if (!paired || T > 64) return 0;
+    const uint32_t P = T / 2;
+    uint32_t label[32];
+    float lo[32][3], hi[32][3], slo[3] = { INFINITY, INFINITY, INFINITY }, shi[3] = { -INFINITY, -INFINITY, -INFINITY };
+    for (uint32_t p = 0; p < P; p++) {
+        label[p] = p;
+        for (int k = 0; k < 3; k++) { lo[p][k] = INFINITY; hi[p][k] = -INFINITY; }
+        for (int a = 0; a < 6; a++)
+            for (int k = 0; k < 3; k++) {
+                float x = v[((size_t)p * 6 + a) * 4 + k];
+                lo[p][k] = fminf(lo[p][k], x); hi[p][k] = fmaxf(hi[p][k], x);
+            }
+        for (int k = 0; k < 3; k++) { slo[k] = fminf(slo[k], lo[p][k]); shi[k] = fmaxf(shi[k], hi[p][k]); }
+    }
+    for (int changed = 1; changed;) {                       /* smallest quad index of the component */
+        changed = 0;
+        for (uint32_t p = 0; p < P; p++)
+            for (uint32_t q = 0; q < P; q++) {
+                if (label[q] >= label[p]) continue;
+                int share = 0;
+                for (int a = 0; a < 6 && !share; a++)
+                    for (int b = 0; b < 6 && !share; b++)
+                        share = !memcmp(v + ((size_t)p * 6 + a) * 4, v + ((size_t)q * 6 + b) * 4, 12);
+                if (share) { label[p] = label[q]; changed = 1; }
+            }
+    }
+    float ext = 0.0f;
+    for (int k = 0; k < 3; k++) ext = fmaxf(ext, shi[k] - slo[k]);
+    const float margin = ext * (1.0f / 128.0f);
+    uint32_t K = 0, always = 0;
+    for (uint32_t c = 0; c < P; c++) {                      /* components in the order of their first quad */
+        if (label[c] != c) continue;
+        uint32_t pairs = 0;
+        float glo[3] = { INFINITY, INFINITY, INFINITY }, ghi[3] = { -INFINITY, -INFINITY, -INFINITY };
+        for (uint32_t p = 0; p < P; p++)
+            if (label[p] == c) {
+                pairs |= 1u << p;
+                for (int k = 0; k < 3; k++) { glo[k] = fminf(glo[k], lo[p][k]); ghi[k] = fmaxf(ghi[k], hi[p][k]); }
+            }
+        int spans = 1, lit = 0;
+        for (int k = 0; k < 3; k++) spans = spans && (ghi[k] - glo[k] >= 0.9f * (shi[k] - slo[k]));
+        for (uint32_t l = 0; l < L; l++) {
+            const float *ctr = (const float *)&lights[l].center;
+            int in = 1;
+            for (int k = 0; k < 3; k++) in = in && ctr[k] >= glo[k] - margin && ctr[k] <= ghi[k] + margin;
+            lit = lit || in;
+        }
+        if (!spans && !lit && K < RT_MAX_GROUPS) {
+            float *r = (float *)out + 4 + 8 * K;
+            for (int k = 0; k < 3; k++) { r[k] = (glo[k] + ghi[k]) * 0.5f; r[4 + k] = (ghi[k] - glo[k]) * 0.5f + margin; }
+            out[4 + 8 * K + 3] = pairs;
+            K++;
+        } else {
+            always |= pairs;
+        }
+    }
+    out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u;
+    return (int)K;
+}
+
+/* csrc/sorted.cuh: ray_clear_of_box, w = box centre - origin */
+static int ray_clear_of_box(const float w[3], const float H[3], const float d[3]) {
+    const float ax = fabsf(d[0]), ay = fabsf(d[1]), az = fabsf(d[2]);
+    int clear = fabsf(fmaf(w[1], d[2], -(w[2] * d[1]))) > fmaf(H[1], az, H[2] * ay);
+    clear |= fabsf(fmaf(w[2], d[0], -(w[0] * d[2]))) > fmaf(H[2], ax, H[0] * az);
+    clear |= fabsf(fmaf(w[0], d[1], -(w[1] * d[0]))) > fmaf(H[0], ay, H[1] * ax);
+    clear |= rt_dot3(w[0], w[1], w[2], d[0], d[1], d[2]) + fmaf(H[2], az, fmaf(H[1], ay, H[0] * ax)) < 0.0f;
+    return clear;
+}
+
+static struct {
+    uint32_t words[RT_GROUP_WORDS];
+    const float *vertices; uint32_t T;
+    uint64_t queries, mismatches, culledTests, fullTests;
+    uint64_t keysDual[16], keysSingle[16];
+} g_chk;
+static _Thread_local int t_pending; static _Thread_local float t_origin[3]; static _Thread_local uint32_t t_key;
+
+static void cull_hook(const float o[3], const float d[3], float tmin, float tmax, int any,
+                      int hit, float distance, uint32_t primitive_id) {
+    const uint32_t K = g_chk.words[0];
+    uint32_t key = 0, pairs = g_chk.words[1];
+    for (uint32_t g = 0; g < K; g++) {
+        const float *r = (const float *)g_chk.words + 4 + 8 * g;
+        const float w[3] = { r[0] - o[0], r[1] - o[1], r[2] - o[2] };
+        if (!ray_clear_of_box(w, r + 4, d)) { key |= 1u << g; pairs |= g_chk.words[4 + 8 * g + 3]; }
+    }
+    int h = 0; uint32_t id = 0, tests = 0;
+    float bestN = tmax, bestD = 1.0f;
+    for (uint32_t i = 0; i < g_chk.T; i++) {
+        if (!((pairs >> (i / 2)) & 1u)) continue;
+        const float *v = g_chk.vertices + (size_t)i * 12;
+        tests++;
+        if (rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &bestN, &bestD)) { h = 1; id = i; if (any) break; }
+    }
+    const float dist = h ? bestN / bestD : 0.0f;
+    const int bad = any ? (h != hit) : (h != hit || (h && (id != primitive_id || memcmp(&dist, &distance, 4))));
+#pragma omp atomic
+    g_chk.queries++;
+    if (bad) {
+#pragma omp atomic
+        g_chk.mismatches++;
+    }
+#pragma omp atomic
+    g_chk.culledTests += tests;
+#pragma omp atomic
+    g_chk.fullTests += g_chk.T;
+    /* the keys the kernel sorts by: a bounce's shadow ray and continuation ray start at one point and share a key;
+     * the last bounce has a shadow ray only */
+    if (any) {
+        if (t_pending) {
+#pragma omp atomic
+            g_chk.keysSingle[t_key]++;
+        }
+        t_pending = 1; memcpy(t_origin, o, 12); t_key = key;
+    } else {
+        if (t_pending && !memcmp(t_origin, o, 12)) {
+#pragma omp atomic
+            g_chk.keysDual[t_key | key]++;
+        } else if (t_pending) {
+#pragma omp atomic
+            g_chk.keysSingle[t_key]++;
+        }
+        t_pending = 0;
+    }
+}
+
+/* stats: queries, mismatches, triangle tests with culling, without, then keysDual[16], keysSingle[16] */
+int rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                        const simd_float3 *vertices, const uint32_t *offsets, float *out,
+                        const RTLaunchParams *params, uint64_t stats[36], int nthreads) {
+    memset(&g_chk, 0, sizeof g_chk);
+    rt_oracle_groups(vertices, params->numTriangles, lights, params->numLights, g_chk.words);
+    g_chk.vertices = (const float *)vertices; g_chk.T = params->numTriangles;
+    rt_oracle_query_hook = cull_hook;
+    uint64_t cnt[RT_CNT_COUNT];
+    int rc = rt_oracle_pathtrace(cameras, materials, lights, vertices, 0, offsets, out, params, cnt, nthreads);
+    rt_oracle_query_hook = 0;
+    stats[0] = g_chk.queries; stats[1] = g_chk.mismatches; stats[2] = g_chk.culledTests; stats[3] = g_chk.fullTests;
+    for (int k = 0; k < 16; k++) { stats[4 + k] = g_chk.keysDual[k]; stats[20 + k] = g_chk.keysSingle[k]; }
+    return rc;
+}

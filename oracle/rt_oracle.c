@@ -162,10 +162,16 @@ typedef struct {
     int bounces;
 } scene_view;
 
+/* Test hook (rt_groups.c: the group-culling checker sees every ray query of a frame and its answer); NULL otherwise. */
+void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
+                             int hit, float distance, uint32_t primitive_id) = 0;
+
 static inline rt_hit scene_intersect(const scene_view *sc, f3 o, f3 d, float tmin, float tmax, int any) {
     float oo[3] = { o.x, o.y, o.z }, dd[3] = { d.x, d.y, d.z };
-    return rt_intersect((const float *)sc->vertices, sc->T, (const float *)sc->spheres, sc->S,
-                        oo, dd, tmin, tmax, any);
+    rt_hit h = rt_intersect((const float *)sc->vertices, sc->T, (const float *)sc->spheres, sc->S,
+                            oo, dd, tmin, tmax, any);
+    if (rt_oracle_query_hook) rt_oracle_query_hook(oo, dd, tmin, tmax, any, h.hit, h.distance, h.primitive_id);
+    return h;
 }
 
 /* One camera sample: raytrace.metal:37-102.  Returns accumulatedColor. */

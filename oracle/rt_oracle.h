@@ -84,6 +84,15 @@ void rt_fixture_spheres(int width, int height, uint32_t seed, uint32_t numSphere
  * offsets[(y-row0)*width+x] = hash(y*width+x + 0x9E3779B9*seed) & 0xFFFFF. */
 void rt_fixture_offsets(uint32_t *offsets, int width, int row0, int rows, uint32_t seed);
 
+/* ---- object groups of the sorted kernel (rt_groups.c) ------------------------ */
+/* out: the 36 words of the prepared scene's "group" section (csrc/rt_scene_layout.h); returns K */
+int  rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L, uint32_t out[36]);
+/* traces the frame and repeats every ray query against the quads group culling leaves: stats = queries,
+ * mismatches (must be 0), triangle tests with / without culling, keysDual[16], keysSingle[16] */
+int  rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                         const simd_float3 *vertices, const uint32_t *offsets, float *out,
+                         const RTLaunchParams *params, uint64_t stats[36], int nthreads);
+
 int  rt_oracle_max_threads(void);
 
 #ifdef __cplusplus

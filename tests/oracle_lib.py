@@ -91,3 +91,25 @@ def flops(cnt, T, S):
     """F = 45*T*(Rc+Rs) + 18*S*(Rc+Rs) + 200*B + 60*P."""
     P, Rc, Rs, B = (int(cnt[i]) for i in range(4))
     return 45 * T * (Rc + Rs) + 18 * S * (Rc + Rs) + 200 * B + 60 * P
+
+
+def groups(scene):
+    """The 36 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
+    out = np.zeros(36, np.uint32)
+    lib.rt_oracle_groups(vp(scene["vertices"]), C.c_uint32(scene["T"]), vp(scene["lights"]), C.c_uint32(scene["L"]), vp(out))
+    return out
+
+
+def cullcheck(scene, width, height, spp, *, bounces=3, seed=1, nthreads=0):
+    """Traces the frame; every ray query is repeated against the quads group culling leaves.
+    Returns dict(queries, mismatches, culled_tests, full_tests, keys_dual[16], keys_single[16])."""
+    off = offsets(width, 0, height, seed)
+    out = np.zeros((height, width, 4), np.float32)
+    stats = np.zeros(36, np.uint64)
+    p = RTLaunchParams(width, height, 0, height, spp, 0, bounces, 0, scene["T"], 0, scene["L"], 6, 300, 0, 0, 0)
+    rc = lib.rt_oracle_cullcheck(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]), vp(scene["vertices"]),
+                                 vp(off), vp(out), C.byref(p), vp(stats), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_cullcheck returned {rc}")
+    return dict(queries=int(stats[0]), mismatches=int(stats[1]), culled_tests=int(stats[2]), full_tests=int(stats[3]),
+                keys_dual=stats[4:20].astype(np.int64), keys_single=stats[20:36].astype(np.int64), image=out)

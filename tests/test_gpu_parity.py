@@ -77,7 +77,7 @@ def test_sincos_and_hash_bit_exact(dev):
     assert np.array_equal(got, np.array([O.lib.rt_oracle_hash(int(v)) for v in u], np.uint32))
 
 
-@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE])
+@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE, L.VARIANT_SORTED])
 def test_config1_cornell_512_16spp(dev, variant):
     """BASELINE.json configs[0]: Cornell 512x512, 16 spp."""
     W = H = 512
@@ -407,3 +407,126 @@ def test_paired_and_unpaired_triangle_loops_agree(dev):
         r = G.Renderer(gsc, W, H, device=dev)
         assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_WAVE), ref), mode
         assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SMEM), ref), mode
+
+
+def _quad(v, t, a, b, c, d):
+    """triangles t, t+1 = (a, b, c), (a, c, d): a quad cut in two on a shared v0, as scene.swift builds them"""
+    f = v.view(np.float32)
+    for k, p in enumerate((a, b, c, a, c, d)):
+        f[(3 * t + k) * 4:(3 * t + k) * 4 + 3] = p
+
+
+def test_sorted_kernel_moved_cameras_bounces_and_sizes(dev):
+    """pathTrace_sorted (csrc/sorted.cuh): the paths of a round sorted by the object groups their rays can reach.
+    Same bits as the oracle for cameras inside the room / in a wall's plane, every bounce count, odd sample counts
+    and ragged sizes, progressive accumulation, and in its ticketed form with sample chunks."""
+    W, H = 96, 64
+    cams = [((0.0, 0.0, 9.0), (0.0, 0.0, -1.0), (0.0, 1.0, 0.0), None),
+            ((0.3, -0.4, 1.0), (0.2, -0.1, -1.0), (0.0, 1.0, 0.0), 1.6),
+            ((2.5, 0.0, 2.0), (-0.3, 0.0, -1.0), (0.0, 1.0, 0.0), 1.2),
+            ((-1.2, 1.9, 0.4), (0.5, -0.8, -0.3), (0.3, 1.0, 0.1), 2.4)]
+    for (pos, direction, up, fov), bounces, spp in zip(cams, (3, 4, 2, 1), (12, 7, 13, 6)):
+        osc = O.cornell(W, H); gsc = G.init_cornell_box(W, H)
+        _set_camera(osc["camera"], pos, direction, up, fov)
+        _set_camera(gsc.camera, pos, direction, up, fov)
+        ref, _ = O.pathtrace(osc, W, H, spp, bounces=bounces)
+        img = G.Renderer(gsc, W, H, device=dev).draw(spp=spp, bounces=bounces, variant=L.VARIANT_SORTED)
+        assert np.array_equal(img, ref), (pos, bounces, int((img != ref).sum()))
+    W, H, spp = 203, 75, 72
+    ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SORTED), ref)
+    r.clear()
+    r.draw_async(spp=41, firstSample=0, accumulate=1, variant=L.VARIANT_SORTED)
+    r.draw_async(spp=31, firstSample=41, accumulate=1, variant=L.VARIANT_SORTED).wait_until_completed()
+    acc = r.image()
+    assert np.all(acc[..., 3] == spp) and np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3])
+
+
+def test_sorted_tiles_with_sample_chunks(dev, monkeypatch):
+    W, H, spp = 200, 77, 72
+    ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    for chunks in ("1", "2", "3", "9"):
+        monkeypatch.setenv("RT_TILES_CHUNKS", chunks)
+        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SORTED_TILES), ref), chunks
+    monkeypatch.delenv("RT_TILES_CHUNKS")
+    assert np.array_equal(r.draw(spp=spp), ref)                      # default: few blocks -> the ticketed sorted form
+    from gpuraytracer_b200 import distributed as D
+    row0, rows, tr, ts = D.tile_params(H, 1, 3, 8)
+    mine = D.local_rows(H, 1, 3, 8)
+    off = np.ascontiguousarray(G.fill_offsets(W, 0, H, seed=1).reshape(H, W)[mine]).reshape(-1)
+    r2 = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev, row0=row0, rows=rows, offsets=off)
+    assert np.array_equal(r2.draw(spp=spp, variant=L.VARIANT_SORTED_TILES, tileRows=tr, tileStride=ts), ref[mine])
+
+
+def test_sorted_kernel_other_groupings(dev):
+    """rt_prep_scene's object groups are whatever the vertices say: scenes whose quads fall into other groups than
+    the Cornell ones (free-floating quads: more groups than key bits; a box welded to the room: fewer; nothing
+    cullable or pairs broken: the kernel's own fall-back to the compacting form) all give the oracle's image."""
+    W, H, spp = 112, 80, 12
+    rng = np.random.default_rng(7)
+    for mode in ("floating", "clusters", "welded", "room_only", "ulp"):
+        osc = O.cornell(W, H); gsc = G.init_cornell_box(W, H)
+        T = 36
+        for sc_v in (osc["vertices"], gsc.vertices):
+            v = sc_v
+            g = np.random.default_rng(11)
+            if mode == "floating":            # the 12 box quads become free quads anywhere in the room
+                for q in range(12):
+                    a = g.uniform(-2.2, 2.2, 3).astype(np.float32)
+                    e1 = g.uniform(-0.9, 0.9, 3).astype(np.float32); e2 = g.uniform(-0.9, 0.9, 3).astype(np.float32)
+                    _quad(v, 10 + 2 * q, a, a + e1, a + e1 + e2, a + e2)
+            elif mode == "clusters":          # three fans of four quads, each fan on one shared corner
+                for c in range(3):
+                    a = g.uniform(-1.8, 1.8, 3).astype(np.float32)
+                    for q in range(4):
+                        e1 = g.uniform(-0.8, 0.8, 3).astype(np.float32); e2 = g.uniform(-0.8, 0.8, 3).astype(np.float32)
+                        _quad(v, 10 + 2 * (4 * c + q), a, a + e1, a + e1 + e2, a + e2)
+            elif mode == "welded":            # one quad of the tall box gets the room's corner as a vertex
+                f = v.view(np.float32)
+                corner = np.array([-2.5, -2.5, -2.5], np.float32)
+                a = f[(3 * 10) * 4:(3 * 10) * 4 + 3].copy(); b = f[(3 * 10 + 1) * 4:(3 * 10 + 1) * 4 + 3].copy()
+                _quad(v, 10, a, b, corner, corner + np.float32(0.5) * (a - b))
+            elif mode == "ulp":
+                v.view(np.uint32)[3 * 4 * 5 + 0] += 1
+        if mode == "room_only":               # walls + light: every group is always tested
+            keep = np.r_[0:10, 34:36]
+            for d_, key in ((osc, "vertices"), (osc, "materials")):
+                d_[key] = np.ascontiguousarray(d_[key].reshape(36, 48)[keep]).reshape(-1)
+            gsc.vertices = np.ascontiguousarray(gsc.vertices.reshape(36, 48)[keep]).reshape(-1)
+            gsc.materials = np.ascontiguousarray(gsc.materials.reshape(36, 48)[keep]).reshape(-1)
+            T = 12; osc["T"] = T; gsc.num_triangles = T
+        assert np.array_equal(osc["vertices"], gsc.vertices)
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        r = G.Renderer(gsc, W, H, device=dev)
+        img = r.draw(spp=spp, variant=L.VARIANT_SORTED)
+        assert np.array_equal(img, ref), (mode, int((img != ref).sum()))
+        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SMEM), ref), mode
+
+
+def test_device_object_groups_match_the_cpu_restatement(dev):
+    """rt_prep_scene's "group" section (boxes, quad masks, always-tested quads) word for word against
+    oracle/rt_groups.c, for the Cornell scene and for scenes with other connectivity."""
+    g = np.random.default_rng(5)
+    scenes = [O.cornell(64, 64)]
+    for mode in ("floating", "clusters", "ulp"):
+        sc = O.cornell(64, 64)
+        if mode == "ulp":
+            sc["vertices"].view(np.uint32)[3 * 4 * 5 + 0] += 1
+        else:
+            a = None
+            for q in range(12):
+                if mode == "floating" or q % 4 == 0:
+                    a = g.uniform(-2.0, 2.0, 3).astype(np.float32)
+                e1 = g.uniform(-0.9, 0.9, 3).astype(np.float32); e2 = g.uniform(-0.9, 0.9, 3).astype(np.float32)
+                _quad(sc["vertices"], 10 + 2 * q, a, a + e1, a + e1 + e2, a + e2)
+        scenes.append(sc)
+    for sc in scenes:
+        T, Lc = sc["T"], sc["L"]
+        v32 = sc["vertices"].view(np.uint32)
+        paired = all(np.array_equal(v32[(3 * i) * 4:(3 * i) * 4 + 3], v32[(3 * (i - 1)) * 4:(3 * (i - 1)) * 4 + 3]) for i in range(1, T, 2))
+        inp = np.concatenate([np.array([T, Lc, int(paired), 0], np.uint32).view(np.uint8), sc["vertices"], sc["lights"]])
+        got = debug_eval(dev, 6, inp, np.zeros(36, np.uint32))
+        want = O.groups(sc)
+        assert np.array_equal(got, want), (got, want)
