@@ -1028,6 +1028,30 @@ RT_SORTED_ENTRY(pathTrace_sorted8, 8, 3)
 /* ticketed (tile, sample chunk) units for launches with few blocks per SM (wave.cuh: RTTileSched) */
 RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
 
+#include "sortedblk.cuh"
+/* the sort taken over the block's four warps (sortedblk.cuh) */
+#define RT_SORTEDBLK_ENTRY(name, R, MINB)                                                                        \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
+            pathtrace_sortedblk_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{});                  \
+        else                                                                                                     \
+            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
+    }
+RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_sortedblk_tiles6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+                           const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,
+                           const RTTileSched ts) {
+    extern __shared__ __align__(16) float sm[];
+    if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])
+        pathtrace_sortedblk_body<6, true>(scene, offsets, out, p, lay, sm, ts);
+    else
+        pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);
+}
+
 #include "modeb.cuh"
 
 /* ----------------------------------------------------------------- resolve ---- */

@@ -1,0 +1,360 @@
+/*
+ * sortedblk.cuh -- sorted.cuh with the sort taken over the whole BLOCK (included by pathtrace.cu after sorted.cuh).
+ *
+ * In sorted.cuh every warp sorts the <= 32 R paths of its own round.  With four key classes and ~170 entries per
+ * bounce, half of the 32-entry chunks mix classes and are traced against the union of their quads: 9.9 quads
+ * per bounce step where the keys alone would need 8.1 (oracle-side count over a frame).  Here the four
+ * warps of a block pool their rounds: 128 R slots, one hit list, one counting sort per bounce (8.65 quads per
+ * step at R = 6), chunks of the sorted list handed to whichever warp is free (a ticket per chunk: chunks cost
+ * 3 to 9 passes of the quad loop depending on their key).  The slots still belong to (warp, sample, lane), so the
+ * camera phase and the in-order accumulation (raytrace.metal:103) are each warp's own; in between, any warp may
+ * trace any path.  Same arithmetic, same bits.
+ *
+ * Price: block barriers (camera | per bounce: A | rank | B) instead of __syncwarp, shared-memory atomics for the
+ * key counters and list appends.
+ */
+#pragma once
+
+template <int R>
+struct SortBlkSmem {
+    static constexpr uint32_t CAP = 32u * R;                                   /* slots per warp */
+    static constexpr uint32_t NSLOT = (RT_BLOCK_THREADS / 32) * CAP;           /* slots per block */
+    static_assert(NSLOT <= 65536u, "slot numbers are 16 bits");
+    /* fields + res.xyz, two 16-bit lists (hit list, sorted list), two byte arrays (surface id, key per slot),
+     * the lanes' offsets, key counters (count + running), three block counters */
+    static constexpr uint32_t WORDS = (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + RT_BLOCK_THREADS + 2u * RT_SORT_KEYS + 4u;
+};
+
+template <int R, bool PERSIST>
+__device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
+                                                         float4 *__restrict__ out, const RTLaunchParams p,
+                                                         const RTSceneLayout lay, float *sm, const RTTileSched ts) {
+    constexpr uint32_t CAP = SortBlkSmem<R>::CAP, NSLOT = SortBlkSmem<R>::NSLOT;
+    {
+        const float4 *src = (const float4 *)scene;
+        float4 *dst = (float4 *)sm;
+        const uint32_t n4 = lay.words >> 2;
+        for (uint32_t k = threadIdx.x; k < n4; k += RT_BLOCK_THREADS) dst[k] = src[k];
+    }
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+
+    float *Q = sm + lay.words;
+    float *res = Q + RT_SORT_FIELDS * NSLOT;
+    uint16_t *hitlist = (uint16_t *)(res + 3 * NSLOT), *sorted = hitlist + NSLOT;
+    uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;
+    uint32_t *offs = (uint32_t *)(keyarr + NSLOT);
+    uint32_t *cnts = offs + RT_BLOCK_THREADS, *run = cnts + RT_SORT_KEYS;
+    uint32_t *ctr = run + RT_SORT_KEYS;                /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
+#define SF(field, s) Q[(field) * NSLOT + (s)]
+    if (threadIdx.x < 2 * RT_SORT_KEYS + 4) cnts[threadIdx.x] = 0u;
+    __syncthreads();
+
+    SceneRef<false> sc;
+    sc.base = (const float4 *)(sm + lay.isect);
+    sc.T = (lay.T + 3u) & ~3u; sc.S = 0u; sc.Treal = lay.T;
+    sc.sph = 4 * lay.Tp;
+
+    const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
+    const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);
+    const f3 cam_v = mk(sm[RT_HDR_CAM_V], sm[RT_HDR_CAM_V + 1], sm[RT_HDR_CAM_V + 2]);
+    const f3 cam_w = mk(sm[RT_HDR_CAM_W], sm[RT_HDR_CAM_W + 1], sm[RT_HDR_CAM_W + 2]);
+    const float halfW = sm[RT_HDR_HALF_W], halfH = sm[RT_HDR_HALF_H];
+    const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
+    const uint32_t nb = (uint32_t)p.bounces;
+    const uint32_t *grp = (const uint32_t *)(sm + lay.group);
+    const uint32_t K = grp[RT_GRP_K];
+    const uint32_t mwT = (lay.T + 31u) >> 5;
+    uint32_t *tail = (uint32_t *)(sm + lay.words + SortBlkSmem<R>::WORDS);
+    /* the quads each key names: always-tested ones + those of the groups whose bit is set */
+    uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1;
+    if (threadIdx.x < RT_SORT_KEYS) {
+        uint32_t pm = grp[RT_GRP_ALWAYS];
+        for (uint32_t g = 0; g < K; g++) if ((threadIdx.x >> g) & 1u) pm |= grp[4 + 8 * g + 3];
+        keyPairs[threadIdx.x] = pm;
+    }
+    __syncthreads();
+
+    for (;;) {
+    uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
+    if (PERSIST) {
+        /* the block's unit comes from a ticket (wave.cuh: RTTileSched) */
+        uint32_t *s_unit = tail + (RT_BLOCK_THREADS / 32) * mwT;
+        __syncthreads();
+        if (threadIdx.x == 0) *s_unit = atomicAdd(ts.counter, 1u);
+        __syncthreads();
+        const uint32_t unit = *s_unit;
+        const uint32_t blocksX = ((uint32_t)p.width + RT_BLOCK_W - 1u) / RT_BLOCK_W, blocksY = ((uint32_t)p.rows + RT_BLOCK_H - 1u) / RT_BLOCK_H;
+        const uint32_t nBlocks = blocksX * blocksY;
+        if (unit >= nBlocks * ts.chunks) break;
+        chunk = unit / nBlocks;
+        const uint32_t bt = unit - chunk * nBlocks;
+        tile = bt * (RT_BLOCK_THREADS / 32) + warp;
+        kBegin = chunk * ts.chunkSpp; kEnd = min(p.spp, kBegin + ts.chunkSpp);
+        x0 = (bt % blocksX) * RT_BLOCK_W + (warp & 1) * 8; ly0 = (bt / blocksX) * RT_BLOCK_H + (warp >> 1) * 4;
+    } else {
+        x0 = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
+    }
+    const uint32_t x = x0 + (lane & 7), ly = ly0 + (lane >> 3);
+    const bool owns = x < (uint32_t)p.width && ly < (uint32_t)p.rows;
+    const uint32_t y = p.tileRows ? (uint32_t)p.row0 + (ly / p.tileRows) * p.tileStride + (ly % p.tileRows)
+                                  : (uint32_t)p.row0 + ly;
+    const size_t pix = (size_t)ly * (uint32_t)p.width + x;
+    const float fx = (float)(int)x, fy = (float)(int)y;
+
+    /* ---- 0. camera-ray candidates of this warp's pixels (pathtrace.cu: camera_candidates) ---- */
+    uint32_t *cullT = tail + warp * mwT;
+    {
+        CameraFrame cf = { cam_o, cam_u, cam_v, cam_w, halfW, halfH, resX, resY };
+        const int big = 0x3fffffff;
+        const int cx0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), cx1 = __reduce_max_sync(0xffffffffu, owns ? (int)x : -big);
+        const int cy0 = __reduce_min_sync(0xffffffffu, owns ? (int)y : big), cy1 = __reduce_max_sync(0xffffffffu, owns ? (int)y : -big);
+        camera_candidates(sc, cf, lay.T, 0u, (float)cx0 - 1.0f, (float)cx1 + 2.0f, (float)cy0 - 1.0f, (float)cy1 + 2.0f,
+                          cullT, mwT, cullT, 0u, lane);
+    }
+
+    const uint32_t offset = owns ? offsets[pix] : 0u;
+    offs[threadIdx.x] = offset;
+    f3 lum = mk(0.0f, 0.0f, 0.0f);
+    if (PERSIST && chunk > 0) {
+        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
+        lum = mk(o.x, o.y, o.z);
+    } else if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
+
+#pragma unroll 1
+    for (uint32_t k0 = kBegin; k0 < kEnd; k0 += R) {
+        const uint32_t nround = min((uint32_t)R, kEnd - k0);                  /* block-uniform */
+        const uint32_t ibase = p.firstSample + k0;
+        /* a warp may start the next round's camera rays while another still reads this round's count: two counters */
+        uint32_t *hits = ctr + (((k0 - kBegin) / R) & 1u);
+
+        /* ---- 1. camera rays: each warp its own pixels, survivors onto the block's hit list ------------- */
+#pragma unroll 1
+        for (uint32_t s = 0; s < nround; s += 2) {
+            const bool two = s + 1 < nround;
+            bool alive[2] = { false, false };
+            uint32_t id[2] = { 0u, 0u };
+            f3 hp[2], r0[2];
+            hp[0] = hp[1] = r0[0] = r0[1] = mk(0.0f, 0.0f, 0.0f);
+            if (owns) {
+                f3 rd[2];
+#pragma unroll
+                for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
+                    const uint32_t idx = offset + (ibase + s + q);
+                    float jx = halton<0>(idx), jy = halton<1>(idx);
+                    float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
+                    float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
+                    rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
+                }
+                bool hit[2]; float dist[2];
+                closest_primary2_list(sc, cullT, mwT, cullT, 0u, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
+                hit[1] = hit[1] && two;
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    if (hit[q]) {
+                        const float *sh = sm + lay.shade + id[q];
+                        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) r0[q] = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
+                        else { alive[q] = true; hp[q] = cam_o + rd[q] * dist[q]; }
+                    }
+                }
+            }
+            const uint32_t m0 = __ballot_sync(0xffffffffu, alive[0]), m1 = __ballot_sync(0xffffffffu, alive[1]);
+            uint32_t base = 0u;
+            if (lane == 0 && (m0 | m1)) base = atomicAdd(hits, (uint32_t)(__popc(m0) + __popc(m1)));
+            base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                if (q == 1 && !two) break;
+                const uint32_t slot = warp * CAP + (s + q) * 32u + lane;
+                if (alive[q]) {
+                    const uint32_t e = base + (q ? __popc(m0) : 0) + __popc((q ? m1 : m0) & lt);
+                    SF(0, slot) = hp[q].x; SF(1, slot) = hp[q].y; SF(2, slot) = hp[q].z;
+                    SF(6, slot) = 1.0f; SF(7, slot) = 1.0f; SF(8, slot) = 1.0f;
+                    hitlist[e] = (uint16_t)slot; idarr[slot] = (uint8_t)id[q];
+                }
+                res[0 * NSLOT + slot] = r0[q].x; res[1 * NSLOT + slot] = r0[q].y; res[2 * NSLOT + slot] = r0[q].z;
+            }
+        }
+        __syncthreads();
+        uint32_t count = *hits;                                                /* hit-list length, block-uniform */
+
+        /* ---- 2. bounces -------------------------------------------------------------------------------- */
+#pragma unroll 1
+        for (uint32_t b = 0; b < nb && count; b++) {
+            const bool cont = b + 1 < nb;
+            const bool sort = count > 32u;          /* one chunk: nothing to sort, the hit list is the order */
+
+            /* -- A. shade set-up, the two rays of the bounce, the key: chunk c of the hit list by warp c % 4 -- */
+#pragma unroll 1
+            for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
+                const uint32_t e = c0 + lane;
+                const bool active = e < count;
+                uint32_t key = 0xffu;
+                if (active) {
+                    const uint32_t slot = hitlist[e], id = idarr[slot];
+                    const uint32_t ow = slot / CAP, os = slot - ow * CAP;      /* owner warp, its slot */
+                    const uint32_t i = offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
+                    const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
+                    f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
+                    const float *sh = sm + lay.shade + id;
+                    const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                    const f3 diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
+                    const f3 P = hp + normal * 1e-3f;                                           /* raytrace.metal:67 */
+                    float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
+                    color = color * diffuse;                                                    /* :76 */
+                    f3 rd = mk(0.0f, 0.0f, 0.0f);
+                    if (cont) {
+                        const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
+                        const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
+                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        f3 sdir = sample_cosine_hemisphere(ux, uy);
+                        rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
+                    }
+                    const float *L = sm + lay.light;
+                    const f3 sp = light_sample_point(mk(L[0], L[1], L[2]), wx, wy);             /* sampling.metal:207-212 */
+                    /* which groups can the two rays reach?  (the box rule does not depend on the length of the
+                     * direction: the shadow ray's is taken un-normalised, B makes the real one) */
+                    const f3 ld = sp - P;
+                    key = 0u;
+                    for (uint32_t g = 0; g < K; g++) {
+                        const float *G = sm + lay.group + 4 + 8 * g;
+                        const f3 w = mk(G[0], G[1], G[2]) - P, H = mk(G[4], G[5], G[6]);
+                        bool clear = ray_clear_of_box(w, H, ld);
+                        if (cont) clear = clear && ray_clear_of_box(w, H, rd);
+                        if (!clear) key |= 1u << g;
+                    }
+                    SF(0, slot) = P.x; SF(1, slot) = P.y; SF(2, slot) = P.z;
+                    if (cont) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
+                    SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
+                    SF(9, slot) = sp.x; SF(10, slot) = sp.z;
+                    keyarr[slot] = (uint8_t)key;
+                }
+                if (sort) {
+                    const uint32_t same = __match_any_sync(0xffffffffu, key);
+                    if (active && lane == (uint32_t)__ffs((int)same) - 1u) atomicAdd(&cnts[key], (uint32_t)__popc(same));
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) { *hits = 0u; ctr[2] = 0u; ctr[3] = 0u; }   /* every thread has read `count` */
+
+            /* -- S. counting sort of the slot numbers, keys descending -- */
+            const uint16_t *order = hitlist;
+            if (sort) {
+                uint32_t start;                                                /* lane j < 16: where key 15 - j starts */
+                {
+                    const uint32_t c = lane < RT_SORT_KEYS ? cnts[RT_SORT_KEYS - 1u - lane] : 0u;
+                    uint32_t incl = c;
+#pragma unroll
+                    for (int d = 1; d < RT_SORT_KEYS; d <<= 1) {
+                        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= (uint32_t)d) incl += up;
+                    }
+                    start = incl - c;
+                }
+#pragma unroll 1
+                for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
+                    const uint32_t e = c0 + lane;
+                    const bool active = e < count;
+                    const uint32_t slot = active ? hitlist[e] : 0u;
+                    const uint32_t key = active ? keyarr[slot] : 0xffu;
+                    const uint32_t same = __match_any_sync(0xffffffffu, key);
+                    const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
+                    uint32_t at = 0u;
+                    if (active && lane == leader) at = atomicAdd(&run[key], (uint32_t)__popc(same));
+                    at = __shfl_sync(0xffffffffu, at, leader) + __shfl_sync(0xffffffffu, start, (RT_SORT_KEYS - 1u - key) & 31u);
+                    if (active) sorted[at + __popc(same & lt)] = (uint16_t)slot;
+                }
+                order = sorted;
+            }
+            __syncthreads();
+            if (sort && threadIdx.x < 2 * RT_SORT_KEYS) cnts[threadIdx.x] = 0u;   /* cnts and run, for the next bounce */
+
+            /* -- B. trace: chunks of the sorted list, a ticket each -- */
+#pragma unroll 1
+            for (;;) {
+                uint32_t c0 = 0u;
+                if (lane == 0) c0 = atomicAdd(&ctr[3], 1u) * 32u;
+                c0 = __shfl_sync(0xffffffffu, c0, 0);
+                if (c0 >= count) break;
+                const uint32_t e = c0 + lane;
+                const bool active = e < count;
+                const uint32_t slot = active ? order[e] : 0u;
+                const uint32_t key = active ? keyarr[slot] : 0u;
+                __syncwarp();                                                  /* (unsorted single chunk: its entries are read before the list is rewritten) */
+                const uint32_t pairs = keyPairs[__reduce_or_sync(0xffffffffu, key)];
+                bool alive = false;
+                uint32_t id = 0;
+                if (active) {
+                    const f3 P = mk(SF(0, slot), SF(1, slot), SF(2, slot));
+                    const float *L = sm + lay.light;
+                    f3 ldir; float ldist, inv;
+                    light_direction(mk(SF(9, slot), L[1], SF(10, slot)), P, ldir, ldist, inv);  /* sampling.metal:214-220 */
+                    const float ltmax = ldist - 1e-3f;                                          /* raytrace.metal:81 */
+                    const uint32_t surf = idarr[slot];
+                    bool shadowed, hitC = false;
+                    float dist = 0.0f;
+                    f3 rd = mk(0.0f, 0.0f, 0.0f);
+                    if (cont) {
+                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
+                        hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);   /* :49, :79-88 */
+                    } else {
+                        shadowed = any_hit_pairs(sc, pairs, P, ldir, 0.0f, ltmax);
+                    }
+                    if (!shadowed) {                                                            /* :74-75, :88 */
+                        const float *sh = sm + lay.shade + surf;
+                        const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                        f3 lightColor = light_colour(mk(L[4], L[5], L[6]), inv, ldir);
+                        lightColor = lightColor * saturate(dot(normal, ldir));
+                        const f3 lc = lightColor * mk(SF(6, slot), SF(7, slot), SF(8, slot));
+                        res[0 * NSLOT + slot] = res[0 * NSLOT + slot] + lc.x;
+                        res[1 * NSLOT + slot] = res[1 * NSLOT + slot] + lc.y;
+                        res[2 * NSLOT + slot] = res[2 * NSLOT + slot] + lc.z;
+                    }
+                    if (hitC) {
+                        const float *sh = sm + lay.shade + id;
+                        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                  /* :59 */
+                            res[0 * NSLOT + slot] = sh[(RT_SH_ER + 0) * lay.Tp]; res[1 * NSLOT + slot] = sh[(RT_SH_ER + 1) * lay.Tp];
+                            res[2 * NSLOT + slot] = sh[(RT_SH_ER + 2) * lay.Tp];
+                        } else {
+                            alive = true;
+                            const f3 hp = P + rd * dist;
+                            SF(0, slot) = hp.x; SF(1, slot) = hp.y; SF(2, slot) = hp.z;
+                        }
+                    }
+                }
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+                uint32_t base = 0u;
+                if (lane == 0 && mask) base = atomicAdd(&ctr[2], (uint32_t)__popc(mask));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (alive) {
+                    hitlist[base + __popc(mask & lt)] = (uint16_t)slot; idarr[slot] = (uint8_t)id;
+                }
+            }
+            __syncthreads();
+            count = ctr[2];
+        }
+        /* (count == 0 when the loop ends -- the last bounce lists no survivors -- so ctr[2] is 0 for the next round) */
+
+        /* ---- 3. in-order accumulation, raytrace.metal:103 ---------------------------------- */
+        for (uint32_t s = 0; s < nround; s++) {
+            const uint32_t slot = warp * CAP + s * 32u + lane;
+            lum = lum + mk(res[0 * NSLOT + slot], res[1 * NSLOT + slot], res[2 * NSLOT + slot]);
+        }
+    }
+
+    if (PERSIST && kEnd < p.spp) {
+        tiles_publish_chunk(ts.flags + tile, chunk, out + pix, make_float4(lum.x, lum.y, lum.z, 0.0f), owns);
+    } else if (owns) {
+        float4 o;
+        if (p.accumulate) {
+            o = make_float4(lum.x, lum.y, lum.z, (float)(p.firstSample + p.spp));
+        } else {
+            float samples = (float)p.spp;                                   /* raytrace.metal:106-109 */
+            o = make_float4(lum.x / samples, lum.y / samples, lum.z / samples, 1.0f);
+        }
+        out[pix] = o;
+    }
+    break;
+    }
+#undef SF
+}

@@ -77,7 +77,7 @@ def test_sincos_and_hash_bit_exact(dev):
     assert np.array_equal(got, np.array([O.lib.rt_oracle_hash(int(v)) for v in u], np.uint32))
 
 
-@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE, L.VARIANT_SORTED])
+@pytest.mark.parametrize("variant", [L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE, L.VARIANT_SORTED, L.VARIANT_SORTED_BLOCK])
 def test_config1_cornell_512_16spp(dev, variant):
     """BASELINE.json configs[0]: Cornell 512x512, 16 spp."""
     W = H = 512
@@ -416,8 +416,10 @@ def _quad(v, t, a, b, c, d):
         f[(3 * t + k) * 4:(3 * t + k) * 4 + 3] = p
 
 
-def test_sorted_kernel_moved_cameras_bounces_and_sizes(dev):
-    """pathTrace_sorted (csrc/sorted.cuh): the paths of a round sorted by the object groups their rays can reach.
+@pytest.mark.parametrize("variant", [L.VARIANT_SORTED, L.VARIANT_SORTED_BLOCK])
+def test_sorted_kernel_moved_cameras_bounces_and_sizes(dev, variant):
+    """pathTrace_sorted (csrc/sorted.cuh; sortedblk.cuh: the sort taken over the block): the paths of a round sorted
+    by the object groups their rays can reach.
     Same bits as the oracle for cameras inside the room / in a wall's plane, every bounce count, odd sample counts
     and ragged sizes, progressive accumulation, and in its ticketed form with sample chunks."""
     W, H = 96, 64
@@ -430,26 +432,27 @@ def test_sorted_kernel_moved_cameras_bounces_and_sizes(dev):
         _set_camera(osc["camera"], pos, direction, up, fov)
         _set_camera(gsc.camera, pos, direction, up, fov)
         ref, _ = O.pathtrace(osc, W, H, spp, bounces=bounces)
-        img = G.Renderer(gsc, W, H, device=dev).draw(spp=spp, bounces=bounces, variant=L.VARIANT_SORTED)
+        img = G.Renderer(gsc, W, H, device=dev).draw(spp=spp, bounces=bounces, variant=variant)
         assert np.array_equal(img, ref), (pos, bounces, int((img != ref).sum()))
     W, H, spp = 203, 75, 72
     ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
     r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
-    assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SORTED), ref)
+    assert np.array_equal(r.draw(spp=spp, variant=variant), ref)
     r.clear()
-    r.draw_async(spp=41, firstSample=0, accumulate=1, variant=L.VARIANT_SORTED)
-    r.draw_async(spp=31, firstSample=41, accumulate=1, variant=L.VARIANT_SORTED).wait_until_completed()
+    r.draw_async(spp=41, firstSample=0, accumulate=1, variant=variant)
+    r.draw_async(spp=31, firstSample=41, accumulate=1, variant=variant).wait_until_completed()
     acc = r.image()
     assert np.all(acc[..., 3] == spp) and np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3])
 
 
-def test_sorted_tiles_with_sample_chunks(dev, monkeypatch):
+@pytest.mark.parametrize("variant", [L.VARIANT_SORTED_TILES, L.VARIANT_SORTED_BLOCK_TILES])
+def test_sorted_tiles_with_sample_chunks(dev, monkeypatch, variant):
     W, H, spp = 200, 77, 72
     ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
     r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
     for chunks in ("1", "2", "3", "9"):
         monkeypatch.setenv("RT_TILES_CHUNKS", chunks)
-        assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SORTED_TILES), ref), chunks
+        assert np.array_equal(r.draw(spp=spp, variant=variant), ref), chunks
     monkeypatch.delenv("RT_TILES_CHUNKS")
     assert np.array_equal(r.draw(spp=spp), ref)                      # default: few blocks -> the ticketed sorted form
     from gpuraytracer_b200 import distributed as D
@@ -457,7 +460,7 @@ def test_sorted_tiles_with_sample_chunks(dev, monkeypatch):
     mine = D.local_rows(H, 1, 3, 8)
     off = np.ascontiguousarray(G.fill_offsets(W, 0, H, seed=1).reshape(H, W)[mine]).reshape(-1)
     r2 = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev, row0=row0, rows=rows, offsets=off)
-    assert np.array_equal(r2.draw(spp=spp, variant=L.VARIANT_SORTED_TILES, tileRows=tr, tileStride=ts), ref[mine])
+    assert np.array_equal(r2.draw(spp=spp, variant=variant, tileRows=tr, tileStride=ts), ref[mine])
 
 
 def test_sorted_kernel_other_groupings(dev):
@@ -500,8 +503,9 @@ def test_sorted_kernel_other_groupings(dev):
         assert np.array_equal(osc["vertices"], gsc.vertices)
         ref, _ = O.pathtrace(osc, W, H, spp)
         r = G.Renderer(gsc, W, H, device=dev)
-        img = r.draw(spp=spp, variant=L.VARIANT_SORTED)
-        assert np.array_equal(img, ref), (mode, int((img != ref).sum()))
+        for variant in (L.VARIANT_SORTED, L.VARIANT_SORTED_BLOCK):
+            img = r.draw(spp=spp, variant=variant)
+            assert np.array_equal(img, ref), (mode, variant, int((img != ref).sum()))
         assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SMEM), ref), mode
 
 
