@@ -1041,6 +1041,10 @@ RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
             pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
     }
 RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)
+#ifdef RT_TUNING_VARIANTS
+RT_SORTEDBLK_ENTRY(pathTrace_exp14, 4, 5)      /* 512 slots, five blocks per SM */
+RT_SORTEDBLK_ENTRY(pathTrace_exp15, 5, 4)
+#endif
 extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
 pathTrace_sortedblk_tiles6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
                            const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,

@@ -203,13 +203,9 @@ __constant__ HaltonTable c_halton = rt_make_halton_table();
 __device__ __noinline__ float halton_rt(uint32_t i, uint32_t d);
 
 /* SLOT 0..3 of bounce b: dimension 2 + 5*b + SLOT (raytrace.metal:72-73,93-94) */
-template <int SLOT>
-__device__ __forceinline__ float halton_slot(uint32_t i, uint32_t bounce) {
-    /* digits needed for i < 2^22 in the smallest base the slot ever sees (bounce 0) */
-    constexpr int DIGITS = rt_digits_for(rt_prime(2 + SLOT), 1ull << 22);
+template <int DIGITS>
+__device__ __forceinline__ float halton_digits(uint32_t i, uint32_t dim) {
     static_assert(DIGITS <= RT_HAL_COLS, "table too narrow");
-    const uint32_t dim = 2u + 5u * bounce + (uint32_t)SLOT;
-    if (i >= (1u << 22)) return halton_rt(i, dim);
     const uint32_t B = c_halton.B[dim], M = c_halton.M[dim];
     float r = 0.0f;
 #pragma unroll
@@ -220,6 +216,16 @@ __device__ __forceinline__ float halton_slot(uint32_t i, uint32_t bounce) {
         i = q;
     }
     return r;
+}
+template <int SLOT>
+__device__ __forceinline__ float halton_slot(uint32_t i, uint32_t bounce) {
+    /* digits needed for i < 2^22: in the slot's base of bounce 0 (5, 7, 11, 13), and in the smallest base any later
+     * bounce gives it (19, 23, 29, 31) -- 31 digit steps per bounce against 21.  The bounce is warp-uniform. */
+    constexpr int DIGITS0 = rt_digits_for(rt_prime(2 + SLOT), 1ull << 22);
+    constexpr int DIGITS1 = rt_digits_for(rt_prime(7 + SLOT), 1ull << 22);
+    const uint32_t dim = 2u + 5u * bounce + (uint32_t)SLOT;
+    if (i >= (1u << 22)) return halton_rt(i, dim);
+    return bounce == 0u ? halton_digits<DIGITS0>(i, dim) : halton_digits<DIGITS1>(i, dim);
 }
 
 /* run-time dimension (self-test and mode B) */

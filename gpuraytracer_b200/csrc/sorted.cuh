@@ -312,9 +312,9 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     }
                     const float *L = sm + lay.light;
                     const f3 sp = light_sample_point(mk(L[0], L[1], L[2]), wx, wy);             /* sampling.metal:207-212 */
-                    f3 ldir; float ldist, inv;
-                    light_direction(sp, P, ldir, ldist, inv);                                   /* repeated in B, bit for bit */
-                    /* which groups can the two rays reach? */
+                    /* which groups can the two rays reach?  (the box rule does not depend on the length of the
+                     * direction: the shadow ray's is taken un-normalised, B makes the real one) */
+                    const f3 ldir = sp - P;
                     key = 0u;
                     for (uint32_t g = 0; g < K; g++) {
                         const float *G = sm + lay.group + 4 + 8 * g;
