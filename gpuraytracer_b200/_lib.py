@@ -26,6 +26,7 @@ INDEX_ACCEL, INDEX_DEBUG, INDEX_SPHERES, INDEX_OUTPUT, INDEX_OFFSETS = 5, 6, 7, 
 FORMAT_RGBA32_FLOAT, FORMAT_R32_UINT = 1, 2
 VARIANT_DEFAULT, VARIANT_SMEM, VARIANT_CONST, VARIANT_WAVE, VARIANT_TILES, VARIANT_WIDE = 0, 1, 2, 3, 16, 17
 VARIANT_SORTED, VARIANT_SORTED_TILES, VARIANT_SORTED_BLOCK, VARIANT_SORTED_BLOCK_TILES = 18, 19, 20, 21
+VARIANT_BVH = 22
 VARIANT_COUNT_RAYS = 0x100
 
 

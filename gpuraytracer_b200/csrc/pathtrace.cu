@@ -1056,6 +1056,8 @@ pathTrace_sortedblk_tiles6(const float *__restrict__ scene, const uint32_t *__re
         pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);
 }
 
+#include "bvh.cuh"
+
 #include "modeb.cuh"
 
 /* ----------------------------------------------------------------- resolve ---- */

@@ -78,7 +78,8 @@
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
 #define RT_CONST_SLOTS   3584
-#define RT_MAX_TRIANGLES 1024
+#define RT_MAX_TRIANGLES 1024            /* brute-force kernels (scene in shared memory) */
+#define RT_MAX_TRIANGLES_BVH (1u << 22)  /* bvh.cuh (scene in global memory) */
 #define RT_MAX_SPHERES   1024
 #define RT_MAX_LIGHTS    16
 

@@ -83,8 +83,10 @@ enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
  * SORTED = WAVE with the paths of a round sorted by the object groups their rays can reach, so that full warps
  * test only those groups' quads (csrc/sorted.cuh; scenes of <= 64 paired triangles, no spheres, one light --
  * per-warp form); SORTED_BLOCK = the same with the sort taken over the block's four warps (csrc/sortedblk.cuh;
- * what DEFAULT picks for the Cornell scene); SORTED_TILES / SORTED_BLOCK_TILES = their ticketed forms */
-enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17, RT_VARIANT_SORTED = 18, RT_VARIANT_SORTED_TILES = 19, RT_VARIANT_SORTED_BLOCK = 20, RT_VARIANT_SORTED_BLOCK_TILES = 21,
+ * what DEFAULT picks for the Cornell scene); SORTED_TILES / SORTED_BLOCK_TILES = their ticketed forms;
+ * BVH = one thread per pixel, every ray query through a bounding-volume hierarchy in global memory (csrc/bvh.cuh,
+ * csrc/host_bvh.h): what DEFAULT picks above 1024 triangles, where the brute-force kernels stop */
+enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17, RT_VARIANT_SORTED = 18, RT_VARIANT_SORTED_TILES = 19, RT_VARIANT_SORTED_BLOCK = 20, RT_VARIANT_SORTED_BLOCK_TILES = 21, RT_VARIANT_BVH = 22,
        RT_VARIANT_COUNT_RAYS = 0x100 };
 
 /* What the reference hard-codes in the shader (raytrace.metal:24-25,

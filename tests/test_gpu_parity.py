@@ -534,3 +534,36 @@ def test_device_object_groups_match_the_cpu_restatement(dev):
         got = debug_eval(dev, 6, inp, np.zeros(36, np.uint32))
         want = O.groups(sc)
         assert np.array_equal(got, want), (got, want)
+
+
+def test_bvh_kernel_small_and_large_scenes(dev):
+    """pathTrace_bvh (csrc/bvh.cuh, host_bvh.cpp): every ray query through a bounding-volume
+    hierarchy instead of the loop over all triangles.  Same image as the oracle's brute-force loop, bit for bit:
+    on the Cornell scene by request (shared edges: the tie rule), and as the library's own choice on a
+    tessellation of it with more triangles (1296, 2304) than the brute-force kernels take."""
+    from bvh_util import tessellate
+    W, H = 96, 64
+    for (pos, direction, up, fov), bounces, spp in (((None, None, None, None), 3, 9),
+                                                    (((0.3, -0.4, 1.0), (0.2, -0.1, -1.0), (0.0, 1.0, 0.0), 1.6), 4, 5)):
+        osc = O.cornell(W, H); gsc = G.init_cornell_box(W, H)
+        if pos is not None:
+            _set_camera(osc["camera"], pos, direction, up, fov); _set_camera(gsc.camera, pos, direction, up, fov)
+        ref, _ = O.pathtrace(osc, W, H, spp, bounces=bounces)
+        img = G.Renderer(gsc, W, H, device=dev).draw(spp=spp, bounces=bounces, variant=L.VARIANT_BVH)
+        assert np.array_equal(img, ref), (pos, int((img != ref).sum()))
+    for n, W, H, spp in ((6, 101, 67, 6), (8, 64, 48, 4)):
+        osc = O.cornell(W, H); gsc = G.init_cornell_box(W, H)
+        tv, tm, T = tessellate(osc["vertices"], osc["materials"], 36, n)
+        osc["vertices"], osc["materials"], osc["T"] = tv, tm, T
+        gsc.vertices, gsc.materials, gsc.num_triangles = tv.copy(), tm.copy(), T
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        r = G.Renderer(gsc, W, H, device=dev)
+        img = r.draw(spp=spp)                                           # T > 1024: the library picks the BVH kernel
+        assert np.array_equal(img, ref), (n, int((img != ref).sum()))
+        assert r.last_command.launch_count() == 3                       # prep, gather, trace
+        # progressive: two launches onto one image, same hierarchy reused
+        r.clear()
+        r.draw_async(spp=spp - 2, firstSample=0, accumulate=1)
+        r.draw_async(spp=2, firstSample=spp - 2, accumulate=1).wait_until_completed()
+        acc = r.image()
+        assert np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3])
