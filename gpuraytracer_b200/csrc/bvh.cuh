@@ -60,7 +60,31 @@ __device__ __forceinline__ f3 bvh_inv(f3 d) {
               fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(1e30f, d.z));
 }
 
-/* closest hit (raytrace.metal:48-49).  `budget` bounds the loop (2 x nodes + 8): a corrupt structure cannot hang. */
+/* One step down the tree: the node's two child boxes against the ray; `limit` = the parameter beyond which a box
+ * cannot matter, as the pair (limN, limD), t = limN / limD.  Sets ref to the next reference to visit (pushing the
+ * farther child when both are hit) or pops; returns false when nothing is left. */
+#define RT_BVH_DONE 0xffffffffu
+__device__ __forceinline__ uint32_t bvh_step(const BvhRef &bv, uint32_t ref, f3 o, f3 inv, float limN, float limD,
+                                             uint32_t *stack, int &sp) {
+    const float4 n0 = bv.nodes[4 * ref], n1 = bv.nodes[4 * ref + 1], n2 = bv.nodes[4 * ref + 2], n3 = bv.nodes[4 * ref + 3];
+    float t0, t1;
+    bool h0 = bvh_box(mk(n0.x, n0.y, n0.z), mk(n1.x, n1.y, n1.z), o, inv, t0);
+    bool h1 = bvh_box(mk(n2.x, n2.y, n2.z), mk(n3.x, n3.y, n3.z), o, inv, t1);
+    h0 = h0 && !(t0 * limD > limN * 1.0001f);            /* beyond the limit?  a NaN keeps */
+    h1 = h1 && !(t1 * limD > limN * 1.0001f);
+    const uint32_t r0 = __float_as_uint(n0.w), r1 = __float_as_uint(n1.w);
+    if (h0 && h1) {
+        const bool swap = t1 < t0;                       /* nearer child first */
+        if (sp < RT_BVH_STACK) stack[sp++] = swap ? r0 : r1;
+        return swap ? r1 : r0;
+    }
+    if (h0 || h1) return h0 ? r0 : r1;
+    return sp ? stack[--sp] : RT_BVH_DONE;
+}
+
+/* closest hit (raytrace.metal:48-49).  "while-while": every lane walks down to its next leaf, then the warp does
+ * its leaves together (one loop mixing both ran 8 of 32 lanes per instruction).  `budget` bounds the walk
+ * (2 x nodes + 8 steps): a corrupt structure cannot hang. */
 __device__ __forceinline__ bool bvh_closest(const BvhRef &bv, f3 o, f3 d, float tmin, float tmax, uint32_t budget,
                                             float &dist, uint32_t &id) {
     const f3 inv = bvh_inv(d);
@@ -69,32 +93,14 @@ __device__ __forceinline__ bool bvh_closest(const BvhRef &bv, f3 o, f3 d, float 
     uint32_t stack[RT_BVH_STACK];
     int sp = 0;
     uint32_t ref = 0u;                                   /* the root is inner node 0 */
-    for (uint32_t it = 0; it < budget; it++) {
-        if (ref & RT_BVH_LEAF_FLAG) {
-            const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
-            for (uint32_t k = 0; k < count; k++) bvh_leaf_closest(bv, first + k, o, d, tmin, bestN, bestD, best);
-            if (sp == 0) break;
-            ref = stack[--sp];
-            continue;
-        }
-        const float4 n0 = bv.nodes[4 * ref], n1 = bv.nodes[4 * ref + 1], n2 = bv.nodes[4 * ref + 2], n3 = bv.nodes[4 * ref + 3];
-        float t0, t1;
-        bool h0 = bvh_box(mk(n0.x, n0.y, n0.z), mk(n1.x, n1.y, n1.z), o, inv, t0);
-        bool h1 = bvh_box(mk(n2.x, n2.y, n2.z), mk(n3.x, n3.y, n3.z), o, inv, t1);
-        /* beyond the best hit so far?  t = bestN / bestD; a NaN keeps */
-        h0 = h0 && !(t0 * bestD > bestN * 1.0001f);
-        h1 = h1 && !(t1 * bestD > bestN * 1.0001f);
-        const uint32_t r0 = __float_as_uint(n0.w), r1 = __float_as_uint(n1.w);
-        if (h0 && h1) {
-            const bool swap = t1 < t0;                   /* nearer child first */
-            if (sp < RT_BVH_STACK) stack[sp++] = swap ? r0 : r1;
-            ref = swap ? r1 : r0;
-        } else if (h0 || h1) {
-            ref = h0 ? r0 : r1;
-        } else {
-            if (sp == 0) break;
-            ref = stack[--sp];
-        }
+    uint32_t it = 0;
+    while (ref != RT_BVH_DONE && it < budget) {
+        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, bestN, bestD, stack, sp); it++; }
+        if (ref == RT_BVH_DONE || !(ref & RT_BVH_LEAF_FLAG)) break;
+        const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
+        for (uint32_t k = 0; k < count; k++) bvh_leaf_closest(bv, first + k, o, d, tmin, bestN, bestD, best);
+        ref = sp ? stack[--sp] : RT_BVH_DONE;
+        it++;
     }
     id = best;
     dist = bestN / bestD;
@@ -106,37 +112,21 @@ __device__ __forceinline__ bool bvh_any(const BvhRef &bv, f3 o, f3 d, float tmin
     const f3 inv = bvh_inv(d);
     uint32_t stack[RT_BVH_STACK];
     int sp = 0;
-    uint32_t ref = 0u;
-    for (uint32_t it = 0; it < budget; it++) {
-        if (ref & RT_BVH_LEAF_FLAG) {
-            const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
-            for (uint32_t k = 0; k < count; k++) {
-                const uint32_t slot = first + k;
-                float N, a;
-                if (tri_test(bv.tris[4 * slot], bv.tris[4 * slot + 1], bv.tris[4 * slot + 2], o, d, tmin, tmax, 1.0f, N, a)) return true;
-            }
-            if (sp == 0) break;
-            ref = stack[--sp];
-            continue;
+    uint32_t ref = 0u, it = 0;
+    bool hit = false;
+    while (ref != RT_BVH_DONE && it < budget) {
+        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, tmax, 1.0f, stack, sp); it++; }
+        if (ref == RT_BVH_DONE || !(ref & RT_BVH_LEAF_FLAG)) break;
+        const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
+        for (uint32_t k = 0; k < count; k++) {
+            const uint32_t slot = first + k;
+            float N, a;
+            hit |= tri_test(bv.tris[4 * slot], bv.tris[4 * slot + 1], bv.tris[4 * slot + 2], o, d, tmin, tmax, 1.0f, N, a);
         }
-        const float4 n0 = bv.nodes[4 * ref], n1 = bv.nodes[4 * ref + 1], n2 = bv.nodes[4 * ref + 2], n3 = bv.nodes[4 * ref + 3];
-        float t0, t1;
-        bool h0 = bvh_box(mk(n0.x, n0.y, n0.z), mk(n1.x, n1.y, n1.z), o, inv, t0);
-        bool h1 = bvh_box(mk(n2.x, n2.y, n2.z), mk(n3.x, n3.y, n3.z), o, inv, t1);
-        h0 = h0 && !(t0 > tmax * 1.0001f);
-        h1 = h1 && !(t1 > tmax * 1.0001f);
-        const uint32_t r0 = __float_as_uint(n0.w), r1 = __float_as_uint(n1.w);
-        if (h0 && h1) {
-            if (sp < RT_BVH_STACK) stack[sp++] = r1;
-            ref = r0;
-        } else if (h0 || h1) {
-            ref = h0 ? r0 : r1;
-        } else {
-            if (sp == 0) break;
-            ref = stack[--sp];
-        }
+        ref = (hit || !sp) ? RT_BVH_DONE : stack[--sp];
+        it++;
     }
-    return false;
+    return hit;
 }
 
 /* leaf slot k <- the intersection record rt_prep_scene made for triangle order[k] (bit for bit) + its id */
