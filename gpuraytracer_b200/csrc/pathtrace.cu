@@ -54,8 +54,35 @@ __device__ __forceinline__ float warp_max(float v) {
     for (int s = 16; s; s >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, s));
     return v;
 }
+/* which quads share a vertex with quad p?  Every warp of the block takes its share of the partners q (lane = p);
+ * the bits are OR-ed into s_adj[p].  (One warp doing all of it took 15 us: three times the rest of the prep kernel,
+ * and a progressive 1-spp frame is only 0.45 ms.) */
+__device__ void prep_adjacency(const unsigned char *__restrict__ vertices, uint32_t P, uint32_t lane, uint32_t warp,
+                               uint32_t nwarps, uint32_t *s_adj) {
+    if (lane >= P) return;
+    const uint32_t *v = (const uint32_t *)vertices;
+    uint32_t vb[18];
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) vb[3 * a + k] = v[(6u * lane + a) * 4u + k];
+    uint32_t adj = 0u;
+    for (uint32_t q = warp; q < P; q += nwarps) {
+        bool share = false;
+#pragma unroll
+        for (int b = 0; b < 6; b++) {
+            const uint32_t x = v[(6u * q + b) * 4u], y = v[(6u * q + b) * 4u + 1u], z = v[(6u * q + b) * 4u + 2u];
+#pragma unroll
+            for (int a = 0; a < 6; a++) share |= vb[3 * a] == x && vb[3 * a + 1] == y && vb[3 * a + 2] == z;
+        }
+        if (share) adj |= 1u << q;
+    }
+    if (adj) atomicOr(&s_adj[lane], adj);
+}
+
 __device__ void prep_groups(const unsigned char *__restrict__ vertices, const unsigned char *__restrict__ lights,
-                            float *__restrict__ scene, const RTSceneLayout lay, bool paired, uint32_t lane) {
+                            float *__restrict__ scene, const RTSceneLayout lay, bool paired, uint32_t lane,
+                            const uint32_t *s_adj) {
     uint32_t *gu = (uint32_t *)scene + lay.group;
     float *gf = scene + lay.group;
     for (uint32_t k = lane; k < RT_GROUP_WORDS; k += 32u) gu[k] = 0u;
@@ -64,27 +91,13 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
     if (!(paired && lay.T >= 2u && lay.T <= 64u && lay.S == 0u)) return;          /* warp-uniform */
     const bool has = lane < P;
     const float INF = __int_as_float(0x7f800000);
-    uint32_t vb[18];
     float lo[3] = { INF, INF, INF }, hi[3] = { -INF, -INF, -INF };
 #pragma unroll
     for (int a = 0; a < 6; a++)
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            vb[3 * a + k] = has ? ((const uint32_t *)vertices)[(6u * lane + a) * 4u + k] : 0u;
-            if (has) { const float x = __uint_as_float(vb[3 * a + k]); lo[k] = fminf(lo[k], x); hi[k] = fmaxf(hi[k], x); }
-        }
-    uint32_t adj = 0u;
-    for (uint32_t q = 0; q < P; q++) {
-        bool share = false;
-#pragma unroll
-        for (int b = 0; b < 6; b++) {
-            const uint32_t x = __shfl_sync(0xffffffffu, vb[3 * b], q), y = __shfl_sync(0xffffffffu, vb[3 * b + 1], q),
-                           z = __shfl_sync(0xffffffffu, vb[3 * b + 2], q);
-#pragma unroll
-            for (int a = 0; a < 6; a++) share |= vb[3 * a] == x && vb[3 * a + 1] == y && vb[3 * a + 2] == z;
-        }
-        if (share && has) adj |= 1u << q;
-    }
+        for (int k = 0; k < 3; k++)
+            if (has) { const float x = ((const float *)vertices)[(6u * lane + a) * 4u + k]; lo[k] = fminf(lo[k], x); hi[k] = fmaxf(hi[k], x); }
+    const uint32_t adj = has ? s_adj[lane] : 0u;
     uint32_t label = lane;
     for (uint32_t it = 0; it < P; it++) {
         uint32_t best = label;
@@ -239,9 +252,14 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             const uint32_t *b = (const uint32_t *)((const SimdF3 *)vertices + 3 * i);
             ok = ok && a[0] == b[0] && a[1] == b[1] && a[2] == b[2];
         }
+        __shared__ uint32_t s_adj[32];
+        if (tid < 32) s_adj[tid] = 0u;
         ok = __syncthreads_and(ok);
         if (tid == 0) ((uint32_t *)scene)[RT_HDR_PAIRED] = ok ? 1u : 0u;
-        if (tid < 32) prep_groups(vertices, lights, scene, lay, ok != 0, (uint32_t)tid);
+        const bool groupable = ok && lay.T >= 2u && lay.T <= 64u && lay.S == 0u;              /* block-uniform */
+        if (groupable) prep_adjacency(vertices, lay.T / 2u, (uint32_t)tid & 31u, (uint32_t)tid >> 5, (uint32_t)nth >> 5, s_adj);
+        __syncthreads();
+        if (tid < 32) prep_groups(vertices, lights, scene, lay, ok != 0, (uint32_t)tid, s_adj);
     }
     for (uint32_t l = tid; l < lay.L; l += nth) {
         const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
@@ -1101,13 +1119,17 @@ extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, 
     if (what == 6) {
         /* the object groups rt_prep_scene makes of a scene: in = T, L, paired, - (uint32), then 48*T bytes of
          * vertices, then 64*L bytes of lights; out = the RT_GROUP_WORDS words of the "group" section */
-        if (k < 32) {
-            const uint32_t *h = (const uint32_t *)in;
-            RTSceneLayout lay = rtSceneLayout(h[0], 0u, h[1]);
-            lay.group = 0u;
-            const unsigned char *v = (const unsigned char *)in + 16;
-            prep_groups(v, v + 48 * (size_t)h[0], (float *)out, lay, h[2] != 0u, k);
-        }
+        __shared__ uint32_t s_adj[32];
+        if (blockIdx.x) return;
+        const uint32_t *h = (const uint32_t *)in;
+        RTSceneLayout lay = rtSceneLayout(h[0], 0u, h[1]);
+        lay.group = 0u;
+        const unsigned char *v = (const unsigned char *)in + 16;
+        if (k < 32) s_adj[k] = 0u;
+        __syncthreads();
+        if (h[2] != 0u && h[0] >= 2u && h[0] <= 64u) prep_adjacency(v, h[0] / 2u, k & 31u, k >> 5, blockDim.x >> 5, s_adj);
+        __syncthreads();
+        if (k < 32) prep_groups(v, v + 48 * (size_t)h[0], (float *)out, lay, h[2] != 0u, k, s_adj);
         return;
     }
     if (k >= n) return;
