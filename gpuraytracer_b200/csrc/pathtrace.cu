@@ -1059,6 +1059,16 @@ RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
             pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
     }
 RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)
+/* fewer samples per launch than a round has slots (progressive rendering): G = 6 / spp tiles side by side per warp */
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_sortedblk_wide6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+                          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {
+    extern __shared__ __align__(16) float sm[];
+    if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])
+        pathtrace_sortedblk_body<6, false, true>(scene, offsets, out, p, lay, sm, RTTileSched{});
+    else
+        pathtrace_wave_body<false, 4, 6, false, true>(scene, offsets, out, p, lay, sm, counters, RTTileSched{});
+}
 #ifdef RT_TUNING_VARIANTS
 RT_SORTEDBLK_ENTRY(pathTrace_exp14, 4, 5)      /* 512 slots, five blocks per SM */
 RT_SORTEDBLK_ENTRY(pathTrace_exp15, 5, 4)

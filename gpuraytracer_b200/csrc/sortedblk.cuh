@@ -15,20 +15,24 @@
  */
 #pragma once
 
-template <int R>
+template <int R, bool SPATIAL = false>
 struct SortBlkSmem {
     static constexpr uint32_t CAP = 32u * R;                                   /* slots per warp */
     static constexpr uint32_t NSLOT = (RT_BLOCK_THREADS / 32) * CAP;           /* slots per block */
     static_assert(NSLOT <= 65536u, "slot numbers are 16 bits");
     /* fields + res.xyz, two 16-bit lists (hit list, sorted list), two byte arrays (surface id, key per slot),
      * the lanes' offsets, key counters (count + running), three block counters */
-    static constexpr uint32_t WORDS = (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + RT_BLOCK_THREADS + 2u * RT_SORT_KEYS + 4u;
+    /* SPATIAL (fewer samples per launch than R: G = R / spp pixel tiles side by side per warp, as pathTrace_wide):
+     * the Halton index of every slot instead of one offset per lane */
+    static constexpr uint32_t OFFS = SPATIAL ? NSLOT : RT_BLOCK_THREADS;
+    static constexpr uint32_t WORDS = (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + OFFS + 2u * RT_SORT_KEYS + 4u;
 };
 
-template <int R, bool PERSIST>
+template <int R, bool PERSIST, bool SPATIAL = false>
 __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                          float4 *__restrict__ out, const RTLaunchParams p,
                                                          const RTSceneLayout lay, float *sm, const RTTileSched ts) {
+    static_assert(!(PERSIST && SPATIAL), "one or the other");
     constexpr uint32_t CAP = SortBlkSmem<R>::CAP, NSLOT = SortBlkSmem<R>::NSLOT;
     {
         const float4 *src = (const float4 *)scene;
@@ -44,7 +48,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     uint16_t *hitlist = (uint16_t *)(res + 3 * NSLOT), *sorted = hitlist + NSLOT;
     uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;
     uint32_t *offs = (uint32_t *)(keyarr + NSLOT);
-    uint32_t *cnts = offs + RT_BLOCK_THREADS, *run = cnts + RT_SORT_KEYS;
+    uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + RT_SORT_KEYS;
     uint32_t *ctr = run + RT_SORT_KEYS;                /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
 #define SF(field, s) Q[(field) * NSLOT + (s)]
     if (threadIdx.x < 2 * RT_SORT_KEYS + 4) cnts[threadIdx.x] = 0u;
@@ -65,7 +69,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     const uint32_t *grp = (const uint32_t *)(sm + lay.group);
     const uint32_t K = grp[RT_GRP_K];
     const uint32_t mwT = (lay.T + 31u) >> 5;
-    uint32_t *tail = (uint32_t *)(sm + lay.words + SortBlkSmem<R>::WORDS);
+    uint32_t *tail = (uint32_t *)(sm + lay.words + SortBlkSmem<R, SPATIAL>::WORDS);
     /* the quads each key names: always-tested ones + those of the groups whose bit is set */
     uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1;
     if (threadIdx.x < RT_SORT_KEYS) {
@@ -75,6 +79,9 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     }
     __syncthreads();
 
+    /* SPATIAL: the warp takes G tiles side by side (sub-tile t = pixels x + 8t); slot j of its one round is sample
+     * j % spp of sub-tile j / spp (wave.cuh) */
+    const uint32_t G = SPATIAL ? max(1u, (uint32_t)R / max(p.spp, 1u)) : 1u;
     for (;;) {
     uint32_t x0, ly0, tile = 0, chunk = 0, kBegin = 0, kEnd = p.spp;
     if (PERSIST) {
@@ -93,8 +100,9 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
         kBegin = chunk * ts.chunkSpp; kEnd = min(p.spp, kBegin + ts.chunkSpp);
         x0 = (bt % blocksX) * RT_BLOCK_W + (warp & 1) * 8; ly0 = (bt / blocksX) * RT_BLOCK_H + (warp >> 1) * 4;
     } else {
-        x0 = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
+        x0 = (blockIdx.x * RT_BLOCK_W + (warp & 1) * 8) * G; ly0 = blockIdx.y * RT_BLOCK_H + (warp >> 1) * 4;
     }
+    if (SPATIAL) kEnd = G * p.spp;                 /* one round: G sub-tiles x spp samples <= R slots */
     const uint32_t x = x0 + (lane & 7), ly = ly0 + (lane >> 3);
     const bool owns = x < (uint32_t)p.width && ly < (uint32_t)p.rows;
     const uint32_t y = p.tileRows ? (uint32_t)p.row0 + (ly / p.tileRows) * p.tileStride + (ly % p.tileRows)
@@ -107,16 +115,18 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     {
         CameraFrame cf = { cam_o, cam_u, cam_v, cam_w, halfW, halfH, resX, resY };
         const int big = 0x3fffffff;
-        const int cx0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), cx1 = __reduce_max_sync(0xffffffffu, owns ? (int)x : -big);
+        const int xr = SPATIAL ? (int)min(x + 8u * (G - 1u), (uint32_t)p.width - 1u) : (int)x;      /* rightmost sub-tile */
+        const int cx0 = __reduce_min_sync(0xffffffffu, owns ? (int)x : big), cx1 = __reduce_max_sync(0xffffffffu, owns ? xr : -big);
         const int cy0 = __reduce_min_sync(0xffffffffu, owns ? (int)y : big), cy1 = __reduce_max_sync(0xffffffffu, owns ? (int)y : -big);
         camera_candidates(sc, cf, lay.T, 0u, (float)cx0 - 1.0f, (float)cx1 + 2.0f, (float)cy0 - 1.0f, (float)cy1 + 2.0f,
                           cullT, mwT, cullT, 0u, lane);
     }
 
     const uint32_t offset = owns ? offsets[pix] : 0u;
-    offs[threadIdx.x] = offset;
+    if (!SPATIAL) offs[threadIdx.x] = offset;
     f3 lum = mk(0.0f, 0.0f, 0.0f);
-    if (PERSIST && chunk > 0) {
+    if (SPATIAL) {
+    } else if (PERSIST && chunk > 0) {
         const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
         lum = mk(o.x, o.y, o.z);
     } else if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
@@ -136,19 +146,32 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
             uint32_t id[2] = { 0u, 0u };
             f3 hp[2], r0[2];
             hp[0] = hp[1] = r0[0] = r0[1] = mk(0.0f, 0.0f, 0.0f);
-            if (owns) {
+            bool own[2] = { owns, owns };
+            float fxq[2] = { fx, fx };
+            uint32_t idx[2] = { offset + (ibase + s), offset + (ibase + s + 1u) };
+            if (SPATIAL) {
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    const uint32_t j = s + q, t = j / p.spp, xt = x + 8u * t;
+                    own[q] = owns && xt < (uint32_t)p.width && j < nround;
+                    fxq[q] = (float)(int)xt;
+                    idx[q] = (own[q] ? offsets[pix + 8u * t] : 0u) + (p.firstSample + (j - t * p.spp));
+                    if (j < nround) offs[warp * CAP + j * 32u + lane] = idx[q];
+                }
+            }
+            if (own[0] || own[1]) {
                 f3 rd[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
-                    const uint32_t idx = offset + (ibase + s + q);
-                    float jx = halton<0>(idx), jy = halton<1>(idx);
-                    float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
+                    float jx = halton<0>(idx[q]), jy = halton<1>(idx[q]);
+                    float sx = ((fxq[q] + jx) / resX) * 2.0f - 1.0f;
                     float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
                     rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
                 }
                 bool hit[2]; float dist[2];
                 closest_primary2_list(sc, cullT, mwT, cullT, 0u, rd[0], rd[1], 0.001f, 1000.0f, hit[0], dist[0], id[0], hit[1], dist[1], id[1]);
-                hit[1] = hit[1] && two;
+                hit[0] = hit[0] && own[0];
+                hit[1] = hit[1] && two && own[1];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {
                     if (hit[q]) {
@@ -193,7 +216,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 if (active) {
                     const uint32_t slot = hitlist[e], id = idarr[slot];
                     const uint32_t ow = slot / CAP, os = slot - ow * CAP;      /* owner warp, its slot */
-                    const uint32_t i = offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
+                    const uint32_t i = SPATIAL ? offs[slot] : offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
                     const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
                     f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
                     const float *sh = sm + lay.shade + id;
@@ -336,13 +359,33 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
         /* (count == 0 when the loop ends -- the last bounce lists no survivors -- so ctr[2] is 0 for the next round) */
 
         /* ---- 3. in-order accumulation, raytrace.metal:103 ---------------------------------- */
-        for (uint32_t s = 0; s < nround; s++) {
-            const uint32_t slot = warp * CAP + s * 32u + lane;
-            lum = lum + mk(res[0 * NSLOT + slot], res[1 * NSLOT + slot], res[2 * NSLOT + slot]);
+        if (SPATIAL) {
+            for (uint32_t t = 0; t < G; t++) {
+                const uint32_t xt = x + 8u * t;
+                if (!(owns && xt < (uint32_t)p.width)) continue;
+                const size_t pt = pix + 8u * t;
+                f3 l = mk(0.0f, 0.0f, 0.0f);
+                if (p.accumulate) { float4 o = out[pt]; l = mk(o.x, o.y, o.z); }
+                for (uint32_t s = t * p.spp; s < (t + 1u) * p.spp; s++) {
+                    const uint32_t slot = warp * CAP + s * 32u + lane;
+                    l = l + mk(res[0 * NSLOT + slot], res[1 * NSLOT + slot], res[2 * NSLOT + slot]);
+                }
+                float4 o;
+                if (p.accumulate) o = make_float4(l.x, l.y, l.z, (float)(p.firstSample + p.spp));
+                else { float samples = (float)p.spp; o = make_float4(l.x / samples, l.y / samples, l.z / samples, 1.0f); }
+                out[pt] = o;
+            }
+        } else {
+            for (uint32_t s = 0; s < nround; s++) {
+                const uint32_t slot = warp * CAP + s * 32u + lane;
+                lum = lum + mk(res[0 * NSLOT + slot], res[1 * NSLOT + slot], res[2 * NSLOT + slot]);
+            }
         }
     }
 
-    if (PERSIST && kEnd < p.spp) {
+    if (SPATIAL) {
+        /* stored per sub-tile above */
+    } else if (PERSIST && kEnd < p.spp) {
         tiles_publish_chunk(ts.flags + tile, chunk, out + pix, make_float4(lum.x, lum.y, lum.z, 0.0f), owns);
     } else if (owns) {
         float4 o;

@@ -567,3 +567,30 @@ def test_bvh_kernel_small_and_large_scenes(dev):
         r.draw_async(spp=2, firstSample=spp - 2, accumulate=1).wait_until_completed()
         acc = r.image()
         assert np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3])
+
+
+def test_sorted_wide_kernel_few_samples_per_launch(dev):
+    """Launches with fewer samples per pixel than a round has slots (progressive rendering) on a groupable scene:
+    the library's choice is pathTrace_sortedblk_wide6 (several tiles side by side per warp, rays sorted by object
+    group).  Bit-equal to the oracle for 1, 2, 3, 5 spp on a ragged size, as a progressive sum of 1-spp frames,
+    and on a scene whose pairing is broken (the kernel's own fall-back to the compacting wide form)."""
+    W, H = 203, 75
+    osc = O.cornell(W, H)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    for spp in (1, 2, 3, 5):
+        ref, _ = O.pathtrace(osc, W, H, spp)
+        img = r.draw(spp=spp)
+        assert np.array_equal(img, ref), (spp, int((img != ref).sum()))
+    frames = 7
+    ref, _ = O.pathtrace(osc, W, H, frames)
+    r.clear()
+    for k in range(frames):
+        cmd = r.draw_async(spp=1, firstSample=k, accumulate=1)
+    cmd.wait_until_completed()
+    acc = r.image()
+    assert np.all(acc[..., 3] == frames) and np.array_equal(acc[..., :3] / np.float32(frames), ref[..., :3])
+    osc2 = O.cornell(W, H); gsc2 = G.init_cornell_box(W, H)
+    for v in (osc2["vertices"], gsc2.vertices):
+        v.view(np.uint32)[3 * 4 * 5 + 0] += 1
+    ref2, _ = O.pathtrace(osc2, W, H, 2)
+    assert np.array_equal(G.Renderer(gsc2, W, H, device=dev).draw(spp=2), ref2)
