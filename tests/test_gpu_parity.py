@@ -594,3 +594,27 @@ def test_sorted_wide_kernel_few_samples_per_launch(dev):
         v.view(np.uint32)[3 * 4 * 5 + 0] += 1
     ref2, _ = O.pathtrace(osc2, W, H, 2)
     assert np.array_equal(G.Renderer(gsc2, W, H, device=dev).draw(spp=2), ref2)
+
+
+def test_prepared_scene_is_reused_until_an_input_changes(dev):
+    """rt_prep_scene runs once per scene, not once per command: a second draw is one launch; changing a material
+    through contents() + did_modify() runs it again and the image follows (same as a fresh renderer's)."""
+    W, H, spp = 96, 64, 8
+    osc = O.cornell(W, H)
+    ref, _ = O.pathtrace(osc, W, H, spp)
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    assert np.array_equal(r.draw(spp=spp), ref) and r.last_command.launch_count() == 2
+    assert np.array_equal(r.draw(spp=spp), ref) and r.last_command.launch_count() == 1
+    assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_SORTED_BLOCK_TILES), ref) and r.last_command.launch_count() == 1
+    # the red wall (triangles 2, 3) turns blue
+    m = r.materials_buffer.contents(np.float32)
+    for t in (2, 3):
+        m[t * 12 + 0], m[t * 12 + 2] = 0.0, 0.9
+    r.materials_buffer.did_modify()
+    om = osc["materials"].view(np.float32)
+    for t in (2, 3):
+        om[t * 12 + 0], om[t * 12 + 2] = 0.0, 0.9
+    ref2, _ = O.pathtrace(osc, W, H, spp)
+    img2 = r.draw(spp=spp)
+    assert r.last_command.launch_count() == 2
+    assert np.array_equal(img2, ref2) and not np.array_equal(ref2, ref)
