@@ -28,6 +28,7 @@ VARIANT_DEFAULT, VARIANT_SMEM, VARIANT_CONST, VARIANT_WAVE, VARIANT_TILES, VARIA
 VARIANT_SORTED, VARIANT_SORTED_TILES, VARIANT_SORTED_BLOCK, VARIANT_SORTED_BLOCK_TILES = 18, 19, 20, 21
 VARIANT_BVH = 22
 VARIANT_COUNT_RAYS = 0x100
+VARIANT_LIGHT_EXTENT = 0x200   # flag: sampleAreaLight over the light's own width x depth
 
 
 class RTLaunchParams(C.Structure):

@@ -201,7 +201,7 @@ pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offs
             for (uint32_t l = 0; l < numLights; l++) {
                 const float *L = lights + RT_LIGHT_WORDS * l;
                 f3 ldir; float ldist;
-                f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+                f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));  /* :75 */
                 if (!bvh_any(bv, P, ldir, 0.0f, ldist - 1e-3f, budget)) acc = acc + lightColor * color;   /* :79-88 */
             }

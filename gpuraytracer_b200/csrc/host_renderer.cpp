@@ -95,6 +95,7 @@ void Renderer::render() {
         RTLaunchParams p;
         check(rtDefaultParams(width, height, &p), "rtDefaultParams");     /* the shader's literals ... */
         p.spp = opt_.spp; p.bounces = opt_.bounces;                       /* ... as parameters */
+        if (opt_.lightExtent) p.variant |= RT_VARIANT_LIGHT_EXTENT;       /* sampling.metal:207-209 with the light's own size */
         p.numTriangles = numTriangles_; p.numSpheres = numSpheres_; p.numLights = numLights_;
         check(rtSetParams(commandBuffer, &p), "rtSetParams");
         check(rtDispatchThreads(commandBuffer, width, height, 1, 8, 8, 1), "dispatchThreads");     /* :137-141 */

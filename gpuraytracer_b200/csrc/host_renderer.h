@@ -29,6 +29,8 @@ struct RenderOptions {
                                         arc4random() % 2^20 (renderer.swift:96-101) so that runs are repeatable */
     bool sphereScene = false;        /* BASELINE config 4 instead of initCornellBox() */
     uint32_t numSpheres = 256;
+    bool lightExtent = false;        /* sample the light's own width x depth (RT_VARIANT_LIGHT_EXTENT) instead of the
+                                        0.5 x 0.5 sampling.metal:207-209 hard-codes */
 };
 
 class Renderer {

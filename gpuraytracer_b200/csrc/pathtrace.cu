@@ -264,8 +264,9 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
     for (uint32_t l = tid; l < lay.L; l += nth) {
         const float *s = (const float *)(lights + 64 * (size_t)l);        /* SquareLightGPU: center@0 color@16 */
         float *d = scene + lay.light + RT_LIGHT_WORDS * l;
-        d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = 0.0f;
-        d[4] = s[4]; d[5] = s[5]; d[6] = s[6]; d[7] = 0.0f;
+        const bool extent = (lay.flags & RT_LAYOUT_LIGHT_EXTENT) != 0u;
+        d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = extent ? 0.5f * s[12] : 0.25f;   /* right.x, sampling.metal:208 */
+        d[4] = s[4]; d[5] = s[5]; d[6] = s[6]; d[7] = extent ? 0.5f * s[13] : 0.25f;   /* up.z,    sampling.metal:209 */
         d[8] = s[8]; d[9] = s[9]; d[10] = s[10]; d[11] = 0.0f;            /* emittedRadiance@32 */
         d[12] = s[12]; d[13] = s[13]; d[14] = 0.0f; d[15] = 0.0f;         /* width@48 depth@52  */
     }
@@ -779,15 +780,17 @@ __device__ __forceinline__ void camera_candidates(const SceneRef<false> &sc, con
 }
 
 /* ---------------------------------------------------------------- shading ---- */
-/* sampling.metal:198-236 with the literals of :207-209 folded:
- * samplePosition = center + (0.25,0,0)*ux + (0,0,0.25)*uy.  The products with the
- * zero components are +-0 and drop out exactly, so only x and z move. */
+/* sampling.metal:198-236 with the zeros of :207-209 folded:
+ * samplePosition = center + (hx,0,0)*ux + (0,0,hz)*uy.  The products with the
+ * zero components are +-0 and drop out exactly, so only x and z move.  (hx,hz) come
+ * from the prepared light (rt_prep_scene): the reference's 0.25, 0.25 unless the
+ * launch asks for the light's own extent (RT_VARIANT_LIGHT_EXTENT). */
 /* the three steps of sampleAreaLight, separately callable (sorted.cuh keeps the sample point and repeats steps
  * 2 and 3 when it traces): the same operations in the same order as the one-piece form below */
-__device__ __forceinline__ f3 light_sample_point(f3 center, float ux, float uy) {
+__device__ __forceinline__ f3 light_sample_point(f3 center, float hx, float hz, float ux, float uy) {
     ux = ux * 2.0f - 1.0f;
     uy = uy * 2.0f - 1.0f;
-    return mk(center.x + 0.25f * ux, center.y, center.z + 0.25f * uy);
+    return mk(center.x + hx * ux, center.y, center.z + hz * uy);
 }
 __device__ __forceinline__ void light_direction(f3 samplePosition, f3 P, f3 &ldir, float &ldist, float &inv) {
     f3 ld = samplePosition - P;
@@ -800,10 +803,10 @@ __device__ __forceinline__ f3 light_colour(f3 lcolor, float inv, f3 ldir) {
     /* dot(-ld, (0,-1,0)) = fma(-z,0, fma(-y,-1, -x*0)) = ld.y (the zero terms are exact) */
     return c * saturate(ldir.y);
 }
-__device__ __forceinline__ f3 sample_area_light(f3 center, f3 lcolor, float ux, float uy, f3 P,
-                                                f3 &ldir, float &ldist) {
+__device__ __forceinline__ f3 sample_area_light(const float *L, float ux, float uy, f3 P, f3 &ldir, float &ldist) {
+    const f3 lcolor = mk(L[4], L[5], L[6]);
     float inv;
-    light_direction(light_sample_point(center, ux, uy), P, ldir, ldist, inv);
+    light_direction(light_sample_point(mk(L[0], L[1], L[2]), L[3], L[7], ux, uy), P, ldir, ldist, inv);
     return light_colour(lcolor, inv, ldir);
 }
 
@@ -928,7 +931,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
             for (uint32_t l = 0; l < numLights; l++) {
                 const float *L = sm + lay.light + RT_LIGHT_WORDS * l;
                 f3 ldir; float ldist;
-                f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+                f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));                          /* :75 */
                 /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
                 if (!any_hit<CONST_BANK, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f))

@@ -69,7 +69,9 @@
 #define RT_SSH_FLAG       6
 #define RT_SSHADE_ROWS    7
 
-#define RT_LIGHT_WORDS   16   /* center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0 */
+#define RT_LIGHT_WORDS   16   /* center.xyz hx | color.xyz hz | emittedRadiance.xyz 0 | width depth 0 0;  (hx,hz) = half extent
+                                 sampleAreaLight uses: 0.25, 0.25 (sampling.metal:207-209) or width/2, depth/2 (RT_LAYOUT_LIGHT_EXTENT) */
+#define RT_LAYOUT_LIGHT_EXTENT 1u
 #define RT_MAX_GROUPS     4   /* cullable object groups (16 sort keys)                                 */
 #define RT_GROUP_WORDS   (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_K          0
@@ -90,6 +92,7 @@ typedef struct RTSceneLayout {
     uint32_t shade, sshade, light;                  /* shading part                               */
     uint32_t words;           /* total size                                          */
     uint32_t group;           /* object groups (sorted.cuh), RT_GROUP_WORDS words    */
+    uint32_t flags;           /* RT_LAYOUT_*: how rt_prep_scene fills the sections   */
 } RTSceneLayout;
 
 #if defined(__CUDACC__)
@@ -111,6 +114,7 @@ RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
     l.group   = l.light + RT_LIGHT_WORDS * L;
     l.words  = l.group + RT_GROUP_WORDS;
     l.words  = (l.words + 3u) & ~3u;
+    l.flags  = 0u;
     return l;
 }
 

@@ -4,6 +4,7 @@
  * plus the knobs BASELINE.json's configs need.  Built as gpuraytracer_b200/rtrace by the Makefile.
  *
  *   rtrace [output.png] [--width W] [--height H] [--spp N] [--bounces B] [--device K] [--seed S] [--spheres]
+ *          [--light-extent]
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -28,6 +29,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(a, "--device")) opt.ordinal = (int)value(a);
         else if (!strcmp(a, "--seed")) opt.seed = (uint32_t)value(a);
         else if (!strcmp(a, "--spheres")) opt.sphereScene = true;
+        else if (!strcmp(a, "--light-extent")) opt.lightExtent = true;
         else if (a[0] == '-') { fprintf(stderr, "unknown option %s\n", a); return 2; }
         else if (!named) { outputFileName = a; named = true; }
     }

@@ -311,7 +311,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
                     }
                     const float *L = sm + lay.light;
-                    const f3 sp = light_sample_point(mk(L[0], L[1], L[2]), wx, wy);             /* sampling.metal:207-212 */
+                    const f3 sp = light_sample_point(mk(L[0], L[1], L[2]), L[3], L[7], wx, wy);             /* sampling.metal:207-212 */
                     /* which groups can the two rays reach?  (the box rule does not depend on the length of the
                      * direction: the shadow ray's is taken un-normalised, B makes the real one) */
                     const f3 ldir = sp - P;

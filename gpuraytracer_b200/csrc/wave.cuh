@@ -292,7 +292,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     if (numLights == 1) {            /* the reference's case: its own straight-line code */
                         const float *L = sm + lay.light;
                         f3 ldir; float ldist;
-                        f3 lightColor = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir, ldist);
+                        f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                         lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
                         bool shadowed;
                         if (paired) {                                                           /* warp-uniform, per launch */
@@ -315,7 +315,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                 if (r < n) {
                                     const float *L = sm + lay.light + RT_LIGHT_WORDS * (l + r);
                                     float ldist;
-                                    lcol[r] = sample_area_light(mk(L[0], L[1], L[2]), mk(L[4], L[5], L[6]), wx, wy, P, ldir[r], ldist);
+                                    lcol[r] = sample_area_light(L, wx, wy, P, ldir[r], ldist);
                                     lcol[r] = lcol[r] * saturate(dot(normal, ldir[r]));             /* :75 */
                                     ltmax[r] = ldist - 1e-3f;
                                 }

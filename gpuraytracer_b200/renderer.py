@@ -102,8 +102,8 @@ class Renderer:
         if self.debug_buffer is not None:
             self.debug_buffer.contents(np.uint64)[:] = 0
             self.debug_buffer.did_modify()
-        v = over.get("variant", 0) & 0xff
-        over["variant"] = (v if v <= L.VARIANT_WAVE else 0) | L.VARIANT_COUNT_RAYS   # tuning variants count with the default kernel
+        v, flags = over.get("variant", 0) & 0xff, over.get("variant", 0) & L.VARIANT_LIGHT_EXTENT
+        over["variant"] = (v if v <= L.VARIANT_WAVE else 0) | L.VARIANT_COUNT_RAYS | flags   # tuning variants count with the default kernel
         self.draw_async(**over).wait_until_completed()
         c = self.debug_buffer.contents(np.uint64)
         return dict(paths=int(c[0]), closest=int(c[1]), shadow=int(c[2]), shaded=int(c[3]))

@@ -85,9 +85,13 @@ enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
  * per-warp form); SORTED_BLOCK = the same with the sort taken over the block's four warps (csrc/sortedblk.cuh;
  * what DEFAULT picks for the Cornell scene); SORTED_TILES / SORTED_BLOCK_TILES = their ticketed forms;
  * BVH = one thread per pixel, every ray query through a bounding-volume hierarchy in global memory (csrc/bvh.cuh,
- * csrc/host_bvh.h): what DEFAULT picks above 1024 triangles, where the brute-force kernels stop */
+ * csrc/host_bvh.h): what DEFAULT picks above 1024 triangles, where the brute-force kernels stop.
+ * Flags above the low byte: COUNT_RAYS (below), and LIGHT_EXTENT: sampleAreaLight takes its sample over the
+ * light's own width x depth, right = (width/2,0,0), up = (0,0,depth/2), instead of the 0.5 x 0.5 the reference
+ * hard-codes (sampling.metal:207-209, the TODO SURVEY N3 names); off = the reference's literals.  Every kernel
+ * form honours it, the image changes with it (the oracle takes the same flag). */
 enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17, RT_VARIANT_SORTED = 18, RT_VARIANT_SORTED_TILES = 19, RT_VARIANT_SORTED_BLOCK = 20, RT_VARIANT_SORTED_BLOCK_TILES = 21, RT_VARIANT_BVH = 22,
-       RT_VARIANT_COUNT_RAYS = 0x100 };
+       RT_VARIANT_COUNT_RAYS = 0x100, RT_VARIANT_LIGHT_EXTENT = 0x200 };
 
 /* What the reference hard-codes in the shader (raytrace.metal:24-25,
  * shaders.metal:644,648) plus the tile / progressive controls BASELINE.json's

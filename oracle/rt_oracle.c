@@ -127,15 +127,18 @@ static inline void camera_ray(const CameraGPU *camera, uint32_t ix, uint32_t iy,
 }
 
 /* sampling.metal:198-236.  The 0.5 x 0.5 extent and the -y normal are the
- * reference's own literals (:207-209); light.width / light.depth are ignored. */
+ * reference's own literals (:207-209); light.width / light.depth are ignored --
+ * unless the caller sets light_extent (RT_VARIANT_LIGHT_EXTENT, SURVEY N3: the
+ * generalisation the TODO of :175 asks for, as directSquareLightRay :180-181 does
+ * it in mode B), when right and up span the light's own width x depth. */
 static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float uy, f3 position,
-                                   f3 *lightDirection, float *lightDistance) {
+                                   f3 *lightDirection, float *lightDistance, int light_extent) {
     ux = ux * 2.0f - 1.0f;
     uy = uy * 2.0f - 1.0f;
 
     f3 normal = f3_make(0.0f, -1.0f, 0.0f);
-    f3 right = f3_make(0.25f, 0.0f, 0.0f);
-    f3 up = f3_make(0.0f, 0.0f, 0.25f);
+    f3 right = f3_make(light_extent ? 0.5f * light->width : 0.25f, 0.0f, 0.0f);
+    f3 up = f3_make(0.0f, 0.0f, light_extent ? 0.5f * light->depth : 0.25f);
     f3 samplePosition = f3_add(f3_add(f3_ld(&light->center), f3_scale(right, ux)), f3_scale(up, uy));
 
     f3 ld = f3_sub(samplePosition, position);
@@ -160,6 +163,7 @@ typedef struct {
     const SphereGPU *spheres;
     uint32_t T, S, L;
     int bounces;
+    int light_extent;
 } scene_view;
 
 /* Test hook (rt_groups.c: the group-culling checker sees every ray query of a frame and its answer); NULL otherwise. */
@@ -218,7 +222,7 @@ static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint
          * same w, one shadow ray each, summed in index order */
         for (uint32_t l = 0; l < sc->L; l++) {
             f3 ldir; float ldist;
-            f3 lightColor = sample_area_light(&sc->lights[l], wx, wy, P, &ldir, &ldist);
+            f3 lightColor = sample_area_light(&sc->lights[l], wx, wy, P, &ldir, &ldist, sc->light_extent);
             lightColor = f3_scale(lightColor, rt_saturate(f3_dot(normal, ldir)));
             /* default-constructed ray: min_distance = 0 (raytrace.metal:79-82) */
             cnt[RT_CNT_SHADOW_RAYS]++;
@@ -257,7 +261,8 @@ int rt_oracle_pathtrace(const CameraGPU *cameras, const MaterialGPU *materials,
     if (p->numSpheres && !spheres) return RT_ERR_INVALID_ARGUMENT;
 
     scene_view sc = { cameras, materials, lights, vertices, spheres,
-                      p->numTriangles, p->numSpheres, p->numLights, p->bounces };
+                      p->numTriangles, p->numSpheres, p->numLights, p->bounces,
+                      (p->variant & RT_VARIANT_LIGHT_EXTENT) != 0 };
     uint64_t total[RT_CNT_COUNT] = { 0 };
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
@@ -316,7 +321,16 @@ void rt_oracle_camera_ray(const CameraGPU *cam, uint32_t x, uint32_t y, float jx
 void rt_oracle_sample_area_light(const SquareLightGPU *light, float ux, float uy, const float pos[3],
                                  float color[3], float ldir[3], float *ldist) {
     f3 d; float dist;
-    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist);
+    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist, 0);
+    color[0] = c.x; color[1] = c.y; color[2] = c.z;
+    ldir[0] = d.x; ldir[1] = d.y; ldir[2] = d.z;
+    *ldist = dist;
+}
+
+void rt_oracle_sample_area_light_ex(const SquareLightGPU *light, float ux, float uy, const float pos[3],
+                                    float color[3], float ldir[3], float *ldist, int light_extent) {
+    f3 d; float dist;
+    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist, light_extent);
     color[0] = c.x; color[1] = c.y; color[2] = c.z;
     ldir[0] = d.x; ldir[1] = d.y; ldir[2] = d.z;
     *ldist = dist;

@@ -58,6 +58,9 @@ void     rt_oracle_camera_ray(const CameraGPU *cam, uint32_t x, uint32_t y, floa
 void     rt_oracle_sample_area_light(const SquareLightGPU *light, float ux, float uy,
                                      const float pos[3], float color[3], float ldir[3],
                                      float *ldist);           /* sampling.metal:198-236 */
+void     rt_oracle_sample_area_light_ex(const SquareLightGPU *light, float ux, float uy,
+                                        const float pos[3], float color[3], float ldir[3],
+                                        float *ldist, int light_extent);   /* with RT_VARIANT_LIGHT_EXTENT */
 void     rt_oracle_cosine_hemisphere(float ux, float uy, const float normal[3], float out[3]);
                                                               /* sampling.metal:39-66   */
 void     rt_oracle_sincos(float x, float *s, float *c);       /* rt_detmath.h           */

@@ -53,8 +53,8 @@ def offsets(width, row0, rows, seed=1):
 
 
 def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, bounces=3, accumulate=False,
-              out=None, off=None, seed=1, nthreads=0, tile_rows=0, tile_stride=0):
-    """Returns (image float32 [rows,width,4], counters uint64[8])."""
+              out=None, off=None, seed=1, nthreads=0, tile_rows=0, tile_stride=0, light_extent=False):
+    """Returns (image float32 [rows,width,4], counters uint64[8]).  light_extent: RT_VARIANT_LIGHT_EXTENT (0x200)."""
     rows = height - row0 if rows is None else rows
     if off is None:
         off = offsets(width, row0, rows, seed)
@@ -62,7 +62,7 @@ def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, b
         out = np.zeros((rows, width, 4), np.float32)
     cnt = np.zeros(8, np.uint64)
     p = RTLaunchParams(width, height, row0, rows, spp, first_sample, bounces, int(accumulate),
-                       scene["T"], scene["S"], scene["L"], 6, 300, 0, tile_rows, tile_stride)
+                       scene["T"], scene["S"], scene["L"], 6, 300, 0x200 if light_extent else 0, tile_rows, tile_stride)
     rc = lib.rt_oracle_pathtrace(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
                                  vp(scene["vertices"]), vp(scene["spheres"]), vp(off), vp(out), C.byref(p),
                                  vp(cnt), nthreads)

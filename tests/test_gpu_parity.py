@@ -618,3 +618,51 @@ def test_prepared_scene_is_reused_until_an_input_changes(dev):
     img2 = r.draw(spp=spp)
     assert r.last_command.launch_count() == 2
     assert np.array_equal(img2, ref2) and not np.array_equal(ref2, ref)
+
+
+def test_light_extent_flag_every_kernel_form(dev):
+    """RT_VARIANT_LIGHT_EXTENT: sampleAreaLight over the light's own width x depth instead of the
+    0.5 x 0.5 of sampling.metal:207-209.  The half extents live in the prepared light (rt_prep_scene), so every kernel
+    form takes them from there: each equals the oracle run with the same flag, bit for bit, and -- same renderer, same
+    buffers -- goes back to the reference's literals when the flag is dropped (the prepared scene is keyed by it)."""
+    W, H, spp = 101, 67, 9
+    osc = O.cornell(W, H)
+    ref0, _ = O.pathtrace(osc, W, H, spp)
+    ref1, cnt1 = O.pathtrace(osc, W, H, spp, light_extent=True)
+    assert not np.array_equal(ref0, ref1)
+    X = L.VARIANT_LIGHT_EXTENT
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    for variant in (L.VARIANT_DEFAULT, L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE, L.VARIANT_TILES, L.VARIANT_SORTED,
+                    L.VARIANT_SORTED_TILES, L.VARIANT_SORTED_BLOCK, L.VARIANT_SORTED_BLOCK_TILES, L.VARIANT_BVH):
+        assert np.array_equal(r.draw(spp=spp, variant=variant | X), ref1), variant
+        assert np.array_equal(r.draw(spp=spp, variant=variant), ref0), variant
+    assert np.array_equal(r.draw(spp=spp, variant=X), ref1) and r.last_command.launch_count() == 2     # flag changed: prep again
+    assert np.array_equal(r.draw(spp=spp, variant=X), ref1) and r.last_command.launch_count() == 1
+    c = r.count_rays(spp=spp, variant=X)
+    assert [c["paths"], c["closest"], c["shadow"], c["shaded"]] == [int(v) for v in cnt1[:4]]
+    for few in (1, 3):                                                 # the wide forms (fewer samples than a round has slots)
+        refw, _ = O.pathtrace(osc, W, H, few, light_extent=True)
+        assert np.array_equal(r.draw(spp=few, variant=X), refw), few
+        assert np.array_equal(r.draw(spp=few, variant=L.VARIANT_WIDE | X), refw), few
+    # config 4's scene with four lights of four sizes (one of them the literal 0.5 x 0.5)
+    W2, H2 = 120, 68
+    osc = O.spheres(W2, H2); gsc = G.init_sphere_scene(W2, H2)
+    for l, wd in enumerate(((0.9, 0.3), (0.2, 1.1), (0.5, 0.5), (1.4, 1.4))):
+        osc["lights"].view(np.float32)[16 * l + 12:16 * l + 14] = wd
+        gsc.lights.view(np.float32)[16 * l + 12:16 * l + 14] = wd
+    ref, _ = O.pathtrace(osc, W2, H2, 4, light_extent=True)
+    lit, _ = O.pathtrace(osc, W2, H2, 4)
+    assert not np.array_equal(ref, lit)
+    r2 = G.Renderer(gsc, W2, H2, device=dev)
+    for variant in (L.VARIANT_DEFAULT, L.VARIANT_SMEM, L.VARIANT_CONST, L.VARIANT_WAVE):
+        assert np.array_equal(r2.draw(spp=4, variant=variant | X), ref), variant
+    assert np.array_equal(r2.draw(spp=4), lit)
+    # a tessellated Cornell scene above the brute-force limit: the BVH kernel by the library's own choice
+    from bvh_util import tessellate
+    W3, H3 = 64, 48
+    osc = O.cornell(W3, H3); gsc = G.init_cornell_box(W3, H3)
+    tv, tm, T = tessellate(osc["vertices"], osc["materials"], 36, 6)
+    osc["vertices"], osc["materials"], osc["T"] = tv, tm, T
+    gsc.vertices, gsc.materials, gsc.num_triangles = tv.copy(), tm.copy(), T
+    ref, _ = O.pathtrace(osc, W3, H3, 4, light_extent=True)
+    assert np.array_equal(G.Renderer(gsc, W3, H3, device=dev).draw(spp=4, variant=X), ref)

@@ -145,3 +145,30 @@ def test_bounces_limit():
         assert False
     except RuntimeError:
         pass
+
+
+def test_light_extent_flag_samples_the_lights_own_rectangle():
+    """RT_VARIANT_LIGHT_EXTENT (the TODO at sampling.metal:175 / the literals of :207-209): right and up
+    span width x depth instead of 0.5 x 0.5.  By hand: a 1 x 2 light at (0, 2.49, 0), u = (1, 0) -> the corner
+    (0.5, 2.49, -1); without the flag (0.25, 2.49, -0.25)."""
+    light = O.cornell(64, 64)["lights"].copy()
+    lf = light.view(np.float32)
+    lf[0:3] = (0.0, 2.49, 0.0); lf[12], lf[13] = 1.0, 2.0
+    col = np.zeros(3, np.float32); ld = np.zeros(3, np.float32); dist = C.c_float()
+    for extent, corner in ((1, (0.5, 2.49, -1.0)), (0, (0.25, 2.49, -0.25))):
+        pos = np.array([corner[0], 0.49, corner[2]], np.float32)          # two units straight below the sample
+        O.lib.rt_oracle_sample_area_light_ex(O.vp(light), C.c_float(1.0), C.c_float(0.0), O.vp(pos), O.vp(col), O.vp(ld),
+                                             C.byref(dist), extent)
+        assert ld.tolist() == [0.0, 1.0, 0.0] and dist.value == np.float32(2.49) - np.float32(0.49)
+        inv = np.float32(1) / np.float32(dist.value)
+        assert np.array_equal(col, lf[4:7] * np.float32(inv * inv))
+    # whole frames: a 0.5 x 0.5 light under the flag is the reference's literal (0.5 * 0.5 = 0.25 exactly) ...
+    W, H, spp = 64, 48, 4
+    sc = O.cornell(W, H)
+    ref, _ = O.pathtrace(sc, W, H, spp)
+    assert sc["lights"].view(np.float32)[12] == 1.0 and sc["lights"].view(np.float32)[13] == 1.0    # scene.swift:23-34
+    wide, cnt_wide = O.pathtrace(sc, W, H, spp, light_extent=True)
+    assert not np.array_equal(wide, ref)                                  # ... the Cornell light is 1 x 1: other samples
+    sc["lights"].view(np.float32)[12:14] = 0.5
+    same, _ = O.pathtrace(sc, W, H, spp, light_extent=True)
+    assert np.array_equal(same, ref)
