@@ -60,12 +60,21 @@ __device__ __forceinline__ f3 bvh_inv(f3 d) {
               fabsf(d.z) > 1e-30f ? 1.0f / d.z : copysignf(1e30f, d.z));
 }
 
+/* The traversal stack of one lane (local memory). */
+struct BvhStack {
+    uint32_t s[RT_BVH_STACK];
+    int sp;
+    __device__ __forceinline__ void reset() { sp = 0; }
+    __device__ __forceinline__ void push(uint32_t v) { if (sp < RT_BVH_STACK) s[sp++] = v; }
+    __device__ __forceinline__ bool empty() const { return sp == 0; }
+    __device__ __forceinline__ uint32_t pop() { return s[--sp]; }
+};
+
 /* One step down the tree: the node's two child boxes against the ray; `limit` = the parameter beyond which a box
- * cannot matter, as the pair (limN, limD), t = limN / limD.  Sets ref to the next reference to visit (pushing the
- * farther child when both are hit) or pops; returns false when nothing is left. */
+ * cannot matter, as the pair (limN, limD), t = limN / limD.  Returns the next reference to visit (pushing the
+ * farther child when both are hit) or pops; RT_BVH_DONE when nothing is left. */
 #define RT_BVH_DONE 0xffffffffu
-__device__ __forceinline__ uint32_t bvh_step(const BvhRef &bv, uint32_t ref, f3 o, f3 inv, float limN, float limD,
-                                             uint32_t *stack, int &sp) {
+__device__ __forceinline__ uint32_t bvh_step(const BvhRef &bv, uint32_t ref, f3 o, f3 inv, float limN, float limD, BvhStack &st) {
     const float4 n0 = bv.nodes[4 * ref], n1 = bv.nodes[4 * ref + 1], n2 = bv.nodes[4 * ref + 2], n3 = bv.nodes[4 * ref + 3];
     float t0, t1;
     bool h0 = bvh_box(mk(n0.x, n0.y, n0.z), mk(n1.x, n1.y, n1.z), o, inv, t0);
@@ -75,31 +84,30 @@ __device__ __forceinline__ uint32_t bvh_step(const BvhRef &bv, uint32_t ref, f3 
     const uint32_t r0 = __float_as_uint(n0.w), r1 = __float_as_uint(n1.w);
     if (h0 && h1) {
         const bool swap = t1 < t0;                       /* nearer child first */
-        if (sp < RT_BVH_STACK) stack[sp++] = swap ? r0 : r1;
+        st.push(swap ? r0 : r1);
         return swap ? r1 : r0;
     }
     if (h0 || h1) return h0 ? r0 : r1;
-    return sp ? stack[--sp] : RT_BVH_DONE;
+    return st.empty() ? RT_BVH_DONE : st.pop();
 }
 
 /* closest hit (raytrace.metal:48-49).  "while-while": every lane walks down to its next leaf, then the warp does
  * its leaves together (one loop mixing both ran 8 of 32 lanes per instruction).  `budget` bounds the walk
  * (2 x nodes + 8 steps): a corrupt structure cannot hang. */
-__device__ __forceinline__ bool bvh_closest(const BvhRef &bv, f3 o, f3 d, float tmin, float tmax, uint32_t budget,
+__device__ __forceinline__ bool bvh_closest(const BvhRef &bv, BvhStack &st, f3 o, f3 d, float tmin, float tmax, uint32_t budget,
                                             float &dist, uint32_t &id) {
     const f3 inv = bvh_inv(d);
     float bestN = tmax, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
-    uint32_t stack[RT_BVH_STACK];
-    int sp = 0;
+    st.reset();
     uint32_t ref = 0u;                                   /* the root is inner node 0 */
     uint32_t it = 0;
     while (ref != RT_BVH_DONE && it < budget) {
-        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, bestN, bestD, stack, sp); it++; }
+        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, bestN, bestD, st); it++; }
         if (ref == RT_BVH_DONE || !(ref & RT_BVH_LEAF_FLAG)) break;
         const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
         for (uint32_t k = 0; k < count; k++) bvh_leaf_closest(bv, first + k, o, d, tmin, bestN, bestD, best);
-        ref = sp ? stack[--sp] : RT_BVH_DONE;
+        ref = st.empty() ? RT_BVH_DONE : st.pop();
         it++;
     }
     id = best;
@@ -108,14 +116,13 @@ __device__ __forceinline__ bool bvh_closest(const BvhRef &bv, f3 o, f3 d, float 
 }
 
 /* any hit (accept_any_intersection, raytrace.metal:79-85): the order of the triangles does not matter */
-__device__ __forceinline__ bool bvh_any(const BvhRef &bv, f3 o, f3 d, float tmin, float tmax, uint32_t budget) {
+__device__ __forceinline__ bool bvh_any(const BvhRef &bv, BvhStack &st, f3 o, f3 d, float tmin, float tmax, uint32_t budget) {
     const f3 inv = bvh_inv(d);
-    uint32_t stack[RT_BVH_STACK];
-    int sp = 0;
+    st.reset();
     uint32_t ref = 0u, it = 0;
     bool hit = false;
     while (ref != RT_BVH_DONE && it < budget) {
-        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, tmax, 1.0f, stack, sp); it++; }
+        while (!(ref & RT_BVH_LEAF_FLAG) && it < budget) { ref = bvh_step(bv, ref, o, inv, tmax, 1.0f, st); it++; }
         if (ref == RT_BVH_DONE || !(ref & RT_BVH_LEAF_FLAG)) break;
         const uint32_t first = ref & 0x07ffffffu, count = ((ref >> 27) & 15u) + 1u;
         for (uint32_t k = 0; k < count; k++) {
@@ -123,7 +130,7 @@ __device__ __forceinline__ bool bvh_any(const BvhRef &bv, f3 o, f3 d, float tmin
             float N, a;
             hit |= tri_test(bv.tris[4 * slot], bv.tris[4 * slot + 1], bv.tris[4 * slot + 2], o, d, tmin, tmax, 1.0f, N, a);
         }
-        ref = (hit || !sp) ? RT_BVH_DONE : stack[--sp];
+        ref = (hit || st.empty()) ? RT_BVH_DONE : st.pop();
         it++;
     }
     return hit;
@@ -142,16 +149,21 @@ extern "C" __global__ void rt_bvh_gather(const float *__restrict__ scene, RTScen
 
 struct RTBvhArgs { const float4 *nodes; const float4 *tris; uint32_t numNodes, pad; };
 
-/* raytrace.metal:11-111 statement by statement (as pathtrace_body), every ray query through the BVH */
-extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
-pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
-              const RTLaunchParams p, const RTSceneLayout lay, const RTBvhArgs ba) {
-    extern __shared__ __align__(16) float sm[];           /* header, then the lights */
+/* raytrace.metal:11-111 statement by statement (as pathtrace_body), every ray query through the BVH.
+ * Measured and not kept (profiles/r03f_bvh_forms.txt; all forms gave the same bits): the sample loop and the bounce
+ * loop merged into one, so that a lane whose path ended starts its pixel's next sample at once (10-18 % SLOWER:
+ * camera rays, which walk the tree together, get mixed with scattered bounce rays), and the traversal stacks in
+ * shared memory instead of local memory (+-2 %).  What pays is residency: six blocks per SM (80 registers, no
+ * spills) against four hide more of the node-fetch latency, +15 to +17 % at 36 to 36 864 triangles. */
+__device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
+                                                   float4 *__restrict__ out, const RTLaunchParams &p, const RTSceneLayout &lay,
+                                                   const RTBvhArgs &ba, float *sm) {
     for (uint32_t k = threadIdx.x; k < RT_HDR_WORDS; k += RT_BLOCK_THREADS) sm[k] = scene[k];
     for (uint32_t k = threadIdx.x; k < RT_LIGHT_WORDS * lay.L; k += RT_BLOCK_THREADS) sm[RT_HDR_WORDS + k] = scene[lay.light + k];
     __syncthreads();
     const float *lights = sm + RT_HDR_WORDS;
     const float *shade = scene + lay.shade;                /* global: SoA rows of Tp words */
+    BvhStack st;
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t x = blockIdx.x * RT_BLOCK_W + (warp & 1) * 8 + (lane & 7);
@@ -185,7 +197,7 @@ pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offs
         f3 ro = cam_o;
         f3 acc = mk(0.0f, 0.0f, 0.0f), color = mk(1.0f, 1.0f, 1.0f);
         float dist; uint32_t id;
-        bool hit = bvh_closest(bv, ro, rd, 0.001f, 1000.0f, budget, dist, id);
+        bool hit = bvh_closest(bv, st, ro, rd, 0.001f, 1000.0f, budget, dist, id);
 #pragma unroll 1
         for (uint32_t b = 0; hit; b++) {                                /* raytrace.metal:47-101 */
             const float *sh = shade + id;
@@ -203,7 +215,7 @@ pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offs
                 f3 ldir; float ldist;
                 f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));  /* :75 */
-                if (!bvh_any(bv, P, ldir, 0.0f, ldist - 1e-3f, budget)) acc = acc + lightColor * color;   /* :79-88 */
+                if (!bvh_any(bv, st, P, ldir, 0.0f, ldist - 1e-3f, budget)) acc = acc + lightColor * color;   /* :79-88 */
             }
             if (b + 1 >= nb) break;
             const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
@@ -212,7 +224,7 @@ pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offs
             f3 sdir = sample_cosine_hemisphere(ux, uy);
             rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;     /* sampling.metal:65 */
             ro = P;                                                     /* :99-100 */
-            hit = bvh_closest(bv, ro, rd, 0.001f, 1000.0f, budget, dist, id);
+            hit = bvh_closest(bv, st, ro, rd, 0.001f, 1000.0f, budget, dist, id);
         }
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
@@ -221,3 +233,18 @@ pathTrace_bvh(const float *__restrict__ scene, const uint32_t *__restrict__ offs
     else { float samples = (float)p.spp; o = make_float4(lum.x / samples, lum.y / samples, lum.z / samples, 1.0f); }
     out[pix] = o;
 }
+
+#define RT_BVH_ENTRY(name, MINB)                                                                                 \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, const RTBvhArgs ba) {                                  \
+        extern __shared__ __align__(16) float sm[];          /* header, then the lights */                       \
+        pathtrace_bvh_body(scene, offsets, out, p, lay, ba, sm);                                                 \
+    }
+RT_BVH_ENTRY(pathTrace_bvh, 6)
+#ifdef RT_TUNING_VARIANTS   /* RT_BVH_FORM=<suffix> (rtcuda.cpp), tools/time_bvh.py: blocks per SM */
+RT_BVH_ENTRY(pathTrace_bvh_l4, 4)
+RT_BVH_ENTRY(pathTrace_bvh_l5, 5)
+RT_BVH_ENTRY(pathTrace_bvh_l7, 7)
+RT_BVH_ENTRY(pathTrace_bvh_l8, 8)
+#endif
