@@ -40,7 +40,6 @@ __device__ __forceinline__ bool bvh_box(f3 lo, f3 hi, f3 o, f3 inv, float &tEnte
 __device__ __forceinline__ void bvh_leaf_closest(const BvhRef &bv, uint32_t slot, f3 o, f3 d, float tmin,
                                                  float &bestN, float &bestD, uint32_t &best) {
     const float4 A = bv.tris[4 * slot], B = bv.tris[4 * slot + 1], C = bv.tris[4 * slot + 2];
-    const uint32_t id = __float_as_uint(bv.tris[4 * slot + 3].x);
     const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
     const f3 w = mk(A.x, A.y, A.z) - o;
     const float D = dot(d, n), Nn = dot(w, n);
@@ -50,8 +49,10 @@ __device__ __forceinline__ void bvh_leaf_closest(const BvhRef &bv, uint32_t slot
     const int t2 = (int)(((__float_as_uint(U) ^ db) | (__float_as_uint(V) ^ db)) | (__float_as_uint(Nn) ^ db));
     const float s = U + V, a = fabsf(D), N = fabsf(Nn);
     const float p1 = N * bestD, p2 = bestN * a;
-    const bool nearer = (p1 < p2) | ((p1 == p2) & (id < best) & (best != 0xffffffffu));
-    if ((t2 >= 0) & (fabsf(s) <= a) & (N >= tmin * a) & nearer) { bestN = N; bestD = a; best = id; }
+    if ((t2 >= 0) & (fabsf(s) <= a) & (N >= tmin * a) & (p1 <= p2)) {       /* (the id is fetched for hits and ties only) */
+        const uint32_t id = __float_as_uint(bv.tris[4 * slot + 3].x);
+        if ((p1 < p2) | ((id < best) & (best != 0xffffffffu))) { bestN = N; bestD = a; best = id; }
+    }
 }
 
 /* 1 / d for the slab test; a zero component becomes +-1e30 so that (plane - origin) * inv is never 0 * inf */
@@ -153,8 +154,9 @@ struct RTBvhArgs { const float4 *nodes; const float4 *tris; uint32_t numNodes, p
  * Measured and not kept (profiles/r03f_bvh_forms.txt; all forms gave the same bits): the sample loop and the bounce
  * loop merged into one, so that a lane whose path ended starts its pixel's next sample at once (10-18 % SLOWER:
  * camera rays, which walk the tree together, get mixed with scattered bounce rays), and the traversal stacks in
- * shared memory instead of local memory (+-2 %).  What pays is residency: six blocks per SM (80 registers, no
- * spills) against four hide more of the node-fetch latency, +15 to +17 % at 36 to 36 864 triangles. */
+ * shared memory instead of local memory (+-2 %).  What pays is residency: more warps hide more of the node-fetch
+ * latency -- six blocks per SM (80 registers) against four +15 to +17 % at 36 to 36 864 triangles, eight (64
+ * registers, 64 bytes of spills) another +3 % (profiles/r03g_bvh_forms.txt). */
 __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                    float4 *__restrict__ out, const RTLaunchParams &p, const RTSceneLayout &lay,
                                                    const RTBvhArgs &ba, float *sm) {
@@ -241,10 +243,9 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
         extern __shared__ __align__(16) float sm[];          /* header, then the lights */                       \
         pathtrace_bvh_body(scene, offsets, out, p, lay, ba, sm);                                                 \
     }
-RT_BVH_ENTRY(pathTrace_bvh, 6)
+RT_BVH_ENTRY(pathTrace_bvh, 8)
 #ifdef RT_TUNING_VARIANTS   /* RT_BVH_FORM=<suffix> (rtcuda.cpp), tools/time_bvh.py: blocks per SM */
 RT_BVH_ENTRY(pathTrace_bvh_l4, 4)
-RT_BVH_ENTRY(pathTrace_bvh_l5, 5)
-RT_BVH_ENTRY(pathTrace_bvh_l7, 7)
-RT_BVH_ENTRY(pathTrace_bvh_l8, 8)
+RT_BVH_ENTRY(pathTrace_bvh_l6, 6)
+RT_BVH_ENTRY(pathTrace_bvh_l10, 10)
 #endif

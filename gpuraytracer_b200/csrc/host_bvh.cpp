@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <limits>
+#include <cstdlib>
 
 namespace {
 struct Box {
@@ -13,14 +14,14 @@ struct Box {
 };
 struct Builder {
     const float *v; std::vector<Box> tb; std::vector<float> cen; std::vector<uint32_t> &order; std::vector<RTBvhNode> &nodes;
-    float margin; int depth;
-    Builder(const float *v_, std::vector<uint32_t> &o, std::vector<RTBvhNode> &n) : v(v_), order(o), nodes(n), margin(0), depth(0) {}
+    float margin; int depth; uint32_t leaf;
+    Builder(const float *v_, std::vector<uint32_t> &o, std::vector<RTBvhNode> &n) : v(v_), order(o), nodes(n), margin(0), depth(0), leaf(RT_BVH_LEAF) {}
     Box bounds(uint32_t b, uint32_t e) const { Box r; r.clear(); for (uint32_t k = b; k < e; k++) r.add(tb[order[k]]); return r; }
     /* builds [b, e): returns its reference and its box */
     uint32_t build(uint32_t b, uint32_t e, Box &box, int d) {
         depth = std::max(depth, d);
         box = bounds(b, e);
-        if (e - b <= RT_BVH_LEAF) return RT_BVH_LEAF_FLAG | ((e - b - 1u) << 27) | b;
+        if (e - b <= leaf) return RT_BVH_LEAF_FLAG | ((e - b - 1u) << 27) | b;
         Box cb; cb.clear();
         for (uint32_t k = b; k < e; k++) cb.add(&cen[3 * (size_t)order[k]]);
         int axis = 0;
@@ -48,6 +49,7 @@ struct Builder {
 int rtBuildBvh(const float *vertices, uint32_t T, std::vector<RTBvhNode> &nodes, std::vector<uint32_t> &order, float *marginOut) {
     nodes.clear(); order.resize(T);
     Builder B(vertices, order, nodes);
+    if (const char *e = getenv("RT_BVH_LEAF")) { const int v = atoi(e); if (v >= 1 && v <= 16) B.leaf = (uint32_t)v; }   /* tuning: tools/time_bvh.py */
     B.tb.resize(T); B.cen.resize(3 * (size_t)T);
     Box scene; scene.clear();
     for (uint32_t i = 0; i < T; i++) {
@@ -63,7 +65,7 @@ int rtBuildBvh(const float *vertices, uint32_t T, std::vector<RTBvhNode> &nodes,
     if (marginOut) *marginOut = B.margin;
     nodes.reserve(T / 2 + 2);
     Box rb;
-    if (T <= RT_BVH_LEAF) {
+    if (T <= B.leaf) {
         /* one leaf: a root whose second child is an empty box */
         RTBvhNode n;
         Box b = T ? B.bounds(0, T) : scene;

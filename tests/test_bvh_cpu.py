@@ -1,5 +1,5 @@
 """The host-side BVH builder (csrc/host_bvh.cpp) without a GPU: every triangle sits in exactly one
-leaf, leaves hold at most four, and every box on the way from the root to a triangle contains it (grown by the margin)."""
+leaf, leaves hold at most twelve, and every box on the way from the root to a triangle contains it (grown by the margin)."""
 import ctypes as C
 
 import numpy as np
@@ -35,7 +35,7 @@ def check_tree(verts, T):
         maxd = max(maxd, d)
         if ref & LEAF:
             first, count = ref & 0x07ffffff, ((ref >> 27) & 15) + 1
-            assert count <= 4
+            assert count <= 12
             for s in range(first, first + count):
                 tri = v[order[s]]
                 assert not seen[order[s]]; seen[order[s]] = True
@@ -53,7 +53,7 @@ def check_tree(verts, T):
 
 def test_builder_on_cornell_and_tessellations():
     sc = O.cornell(64, 64)
-    assert check_tree(sc["vertices"], 36)[0] >= 8
+    assert check_tree(sc["vertices"], 36)[0] >= 3
     for n in (3, 6):
         tv, tm, T = tessellate(sc["vertices"], sc["materials"], 36, n)
         nn, depth = check_tree(tv, T)
@@ -62,7 +62,7 @@ def test_builder_on_cornell_and_tessellations():
 
 def test_builder_small_and_degenerate():
     sc = O.cornell(64, 64)
-    for T in (1, 2, 4, 5):
+    for T in (1, 2, 4, 5, 12, 13, 25):
         check_tree(sc["vertices"][:48 * T].copy(), T)
     same = np.tile(sc["vertices"][:48], 37).copy()        # 37 copies of one triangle: all centroids equal
     check_tree(same, 37)

@@ -12,6 +12,8 @@ W, H, SPP = (int(a) for a in sys.argv[1:4]) if len(sys.argv) >= 4 else (1920, 10
 # image is compared with the shipped kernel's (which the GPU tests compare with the oracle)
 FORMS = [f for f in os.environ.get("BVH_FORMS", "-").split(",") if f]
 SIZES = [int(n) for n in os.environ.get("BVH_SIZES", "1,4,8,16,32").split(",")]
+# BVH_LEAVES="4,2,8": triangles per leaf of the host build (RT_BVH_LEAF), first entry = the image the others are compared with
+LEAVES = [v for v in os.environ.get("BVH_LEAVES", "").split(",") if v]
 dev = G.Device(0)
 base = G.init_cornell_box(W, H)
 for n in SIZES:
@@ -19,11 +21,13 @@ for n in SIZES:
     if n > 1:
         tv, tm, T = tessellate(base.vertices, base.materials, 36, n)
         sc.vertices, sc.materials, sc.num_triangles = tv, tm, T
-    r = G.Renderer(sc, W, H, device=dev)
-    os.environ.pop("RT_BVH_FORM", None)
-    t0 = time.time(); r.draw(spp=2, variant=L.VARIANT_BVH); build_s = time.time() - t0     # includes the host build
     ref = None
-    for form in FORMS:
+    for leaf, form in [(lf, fm) for lf in (LEAVES or [""]) for fm in FORMS]:
+        if leaf:
+            os.environ["RT_BVH_LEAF"] = leaf
+        r = G.Renderer(sc, W, H, device=dev)               # a new queue: a new hierarchy
+        os.environ.pop("RT_BVH_FORM", None)
+        t0 = time.time(); r.draw(spp=2, variant=L.VARIANT_BVH); build_s = time.time() - t0     # includes the host build
         if form == "-":
             os.environ.pop("RT_BVH_FORM", None)
         else:
@@ -36,7 +40,7 @@ for n in SIZES:
         img = r.image()
         if ref is None:
             ref = img
-        line = (f"T = {sc.num_triangles:6d} {form:>4s}: {ms:8.2f} ms  {W * H * SPP / ms / 1e3:8.1f} Mpaths/s  "
+        line = (f"T = {sc.num_triangles:6d} {form:>4s} {('leaf ' + leaf) if leaf else ''}: {ms:8.2f} ms  {W * H * SPP / ms / 1e3:8.1f} Mpaths/s  "
                 f"(first draw incl. host build {build_s * 1e3:.0f} ms)  same image as the first form: {np.array_equal(img, ref)}")
         print(line, flush=True)
     os.environ.pop("RT_BVH_FORM", None)
