@@ -7,6 +7,7 @@
  *                     `pathTrace`, reference RTrace/raytrace.metal:11-111 with
  *                     RTrace/sampling.metal:16-26,39-66,97-157,198-236
  *   rt_resolve_rgba8  RTrace/image.swift:40-65 tone map as a device pass
+ *   rt_resolve_rgba16f  float4 -> half4, the reference's render-target format (renderer.swift:74-82)
  *   rt_debug_eval     evaluates single device functions for bit-compare tests
  *
  * Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -prec-div=true
@@ -19,6 +20,7 @@
  * structure.
  */
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include "../../include/rtcuda.h"
 #include "rt_scene_layout.h"
@@ -1112,6 +1114,20 @@ extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar
         r[k] = (unsigned char)(value * 255.0f);
     }
     out[i] = make_uchar4(r[0], r[1], r[2], 255);
+}
+
+/* The reference's render target is rgba16Float (RTrace/renderer.swift:74-82: the shader's write rounds fp32 to
+ * fp16) and saveTextureToImage reads it back as [Float16] (image.swift:25-38).  This pass gives a host that keeps
+ * that code the same bytes: round-to-nearest-even per channel, alpha as stored (1 after a mean; after
+ * divideByAlpha the resolved progressive image, alpha 1). */
+extern "C" __global__ void rt_resolve_rgba16f(const float4 *__restrict__ in, ushort4 *__restrict__ out,
+                                              unsigned long long n, int divideByAlpha) {
+    unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = in[i];
+    if (divideByAlpha) { v.x = v.x / v.w; v.y = v.y / v.w; v.z = v.z / v.w; v.w = 1.0f; }
+    out[i] = make_ushort4(__half_as_ushort(__float2half_rn(v.x)), __half_as_ushort(__float2half_rn(v.y)),
+                          __half_as_ushort(__float2half_rn(v.z)), __half_as_ushort(__float2half_rn(v.w)));
 }
 
 /* ------------------------------------------------------------------- debug ---- */

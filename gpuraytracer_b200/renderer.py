@@ -122,6 +122,14 @@ class Renderer:
               "rtResolveToRGBA8")
         return out.contents(np.uint8).reshape(self.rows, self.width, 4).copy()
 
+    def resolve_rgba16f(self, divide_by_alpha=False):
+        """The image in the reference's render-target format (rgba16Float, renderer.swift:74-82); float16 [rows, width, 4]."""
+        npx = self.width * self.rows
+        out = self.device.make_buffer(length=npx * 8)
+        check(lib.rtResolveToRGBA16F(self.queue.h, self.render_buffer.h, 0, out.h, 0, npx, int(divide_by_alpha)),
+              "rtResolveToRGBA16F")
+        return out.contents(np.float16).reshape(self.rows, self.width, 4).copy()
+
     def save_png(self, path, divide_by_alpha=False):
         from PIL import Image
         Image.fromarray(self.resolve_rgba8(divide_by_alpha), "RGBA").save(path)

@@ -226,6 +226,11 @@ int rtCommandRelease(RTCommand *command);
  * accumulation buffer (xyz / w) first.  Runs as a small kernel on the queue. */
 int rtResolveToRGBA8(RTQueue *queue, RTBuffer *in, size_t inOffset, RTBuffer *out, size_t outOffset,
                      uint64_t pixelCount, int divideByAlpha);
+/* The same buffer in the reference's render-target format, rgba16Float (renderer.swift:74-82): 8 bytes per pixel,
+ * each channel rounded to nearest-even as the shader's texture write does -- what saveTextureToImage reads back as
+ * [Float16] (image.swift:25-38).  divideByAlpha != 0: xyz / w first, alpha 1. */
+int rtResolveToRGBA16F(RTQueue *queue, RTBuffer *in, size_t inOffset, RTBuffer *out, size_t outOffset,
+                       uint64_t pixelCount, int divideByAlpha);
 
 /* ---- new: one process, several GPUs, row tiles ------------------------------ */
 int rtGroupCreate(const int *ordinals, int count, RTGroup **out);

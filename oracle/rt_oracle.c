@@ -372,6 +372,40 @@ void rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels) 
     }
 }
 
+/* fp32 -> fp16, round to nearest even: what a shader write to the reference's rgba16Float render target does
+ * (RTrace/renderer.swift:74-82) and what image.swift:25-38 reads back.  IEEE 754 binary16 by bit arithmetic. */
+static uint16_t f32_to_f16_rne(float f) {
+    uint32_t x;
+    memcpy(&x, &f, 4);
+    const uint32_t sign = (x >> 16) & 0x8000u, e = (x >> 23) & 0xffu;
+    uint32_t m = x & 0x7fffffu;
+    if (e == 0xffu) return (uint16_t)(sign | 0x7c00u | (m ? 0x200u | (m >> 13) : 0u));     /* inf, NaN (quiet) */
+    const int32_t E = (int32_t)e - 127 + 15;
+    if (E >= 0x1f) return (uint16_t)(sign | 0x7c00u);                                       /* overflow -> inf */
+    if (E <= 0) {                                                                           /* subnormal half or zero */
+        if (E < -10) return (uint16_t)sign;                                                 /* below 2^-25 */
+        m |= 0x800000u;
+        const uint32_t shift = (uint32_t)(14 - E);                                          /* 14 .. 24 */
+        uint32_t h = m >> shift;
+        const uint32_t rem = m & ((1u << shift) - 1u), half = 1u << (shift - 1u);
+        if (rem > half || (rem == half && (h & 1u))) h++;
+        return (uint16_t)(sign | h);
+    }
+    uint32_t h = ((uint32_t)E << 10) | (m >> 13);
+    const uint32_t rem = m & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (h & 1u))) h++;                                 /* a carry may reach inf: correct */
+    return (uint16_t)(sign | h);
+}
+
+/* checker of rtResolveToRGBA16F: float4 -> half4; divide_by_alpha: xyz / w first, alpha 1 */
+void rt_oracle_resolve_rgba16f(const float *rgba, uint16_t *out, uint64_t npixels, int divide_by_alpha) {
+    for (uint64_t i = 0; i < npixels; i++) {
+        float v[4] = { rgba[i * 4], rgba[i * 4 + 1], rgba[i * 4 + 2], rgba[i * 4 + 3] };
+        if (divide_by_alpha) { v[0] = v[0] / v[3]; v[1] = v[1] / v[3]; v[2] = v[2] / v[3]; v[3] = 1.0f; }
+        for (int c = 0; c < 4; c++) out[i * 4 + c] = f32_to_f16_rne(v[c]);
+    }
+}
+
 int rt_oracle_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -70,6 +70,7 @@ int      rt_oracle_intersect(const simd_float3 *vertices, uint32_t numTriangles,
                              int acceptAny, float *distance, uint32_t *primitive_id);
 /* image.swift:40-65: x2 exposure, Reinhard, gamma 2.2 -> RGBA8 */
 void     rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels);
+void     rt_oracle_resolve_rgba16f(const float *rgba, uint16_t *out, uint64_t npixels, int divide_by_alpha);
 
 /* ---- fixtures (restated input data) ---------------------------------------- */
 /* Cornell box of RTrace/scene.swift:14-240: 36 triangles (108 vertices), their 36

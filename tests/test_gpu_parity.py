@@ -159,6 +159,35 @@ def test_resolve_rgba8_matches_image_swift(dev):
     assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and np.all(got[..., 3] == 255)
 
 
+def test_resolve_rgba16f_is_the_reference_render_target_format(dev):
+    """rtResolveToRGBA16F: the fp32 image as the rgba16Float texture the reference renders into (renderer.swift:74-82),
+    every channel rounded to nearest-even -- the [Float16] array image.swift:25-38 reads.  Bit-equal to the oracle's
+    conversion, also from a progressive accumulation buffer (xyz / w, alpha 1) and for values that overflow,
+    underflow and tie."""
+    W, H = 128, 96
+    r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
+    img = r.draw(spp=16)
+    want = np.zeros((H, W, 4), np.uint16)
+    O.lib.rt_oracle_resolve_rgba16f(O.vp(img), O.vp(want), C.c_uint64(W * H), 0)
+    got = r.resolve_rgba16f()
+    assert np.array_equal(got.view(np.uint16), want) and np.all(got[..., 3] == 1.0)
+    r.clear()
+    r.draw_async(spp=5, firstSample=0, accumulate=1)
+    r.draw_async(spp=3, firstSample=5, accumulate=1).wait_until_completed()
+    acc = r.image()
+    O.lib.rt_oracle_resolve_rgba16f(O.vp(acc), O.vp(want), C.c_uint64(W * H), 1)
+    assert np.array_equal(r.resolve_rgba16f(divide_by_alpha=True).view(np.uint16), want)
+    # arbitrary bit patterns through the same pass (no NaNs: their payload is not part of the contract)
+    bits = np.random.default_rng(3).integers(0, 1 << 32, W * H * 4, dtype=np.uint64).astype(np.uint32)
+    vals = bits.view(np.float32).copy()
+    vals[np.isnan(vals)] = 65520.0
+    vals[:8] = (1.0 + 2.0 ** -11, 1.0 + 3 * 2.0 ** -11, 65520.0, 2.0 ** -25, 6e-8, -2.0, 65504.0, 0.0)
+    r.render_buffer.contents(np.float32)[:] = vals
+    r.render_buffer.did_modify()
+    O.lib.rt_oracle_resolve_rgba16f(O.vp(vals), O.vp(want), C.c_uint64(W * H), 0)
+    assert np.array_equal(r.resolve_rgba16f().view(np.uint16), want)
+
+
 def test_error_paths(dev):
     with pytest.raises(G.RTError) as e:
         dev.make_pipeline("noSuchKernel")

@@ -172,3 +172,26 @@ def test_light_extent_flag_samples_the_lights_own_rectangle():
     sc["lights"].view(np.float32)[12:14] = 0.5
     same, _ = O.pathtrace(sc, W, H, spp, light_extent=True)
     assert np.array_equal(same, ref)
+
+
+def test_half_resolve_is_ieee_round_to_nearest_even():
+    """rt_oracle_resolve_rgba16f (the checker of rtResolveToRGBA16F; the reference's render target is rgba16Float,
+    renderer.swift:74-82): by hand 1 + 2^-11 ties to 1.0 (0x3C00), 1 + 3 * 2^-11 ties to 1 + 2^-9 (0x3C02), 65520 -> inf,
+    2^-25 -> 0, anything above it -> the smallest subnormal; and numpy's float16 cast agrees on 2^20 random bit patterns."""
+    def half(values, divide=0):
+        f = np.asarray(values, np.float32).reshape(-1, 4).copy()
+        out = np.zeros(f.shape, np.uint16)
+        O.lib.rt_oracle_resolve_rgba16f(O.vp(f), O.vp(out), C.c_uint64(len(f)), divide)
+        return out
+    e = half([1.0 + 2.0 ** -11, 1.0 + 3 * 2.0 ** -11, 65520.0, 2.0 ** -25,
+              np.float32(2.0 ** -25) * np.float32(1.0000001), -2.0, 65504.0, 0.0])
+    assert e.reshape(-1).tolist() == [0x3C00, 0x3C02, 0x7C00, 0x0000, 0x0001, 0xC000, 0x7BFF, 0x0000]
+    bits = np.random.default_rng(7).integers(0, 1 << 32, 1 << 20, dtype=np.uint64).astype(np.uint32)
+    f = bits.view(np.float32)
+    with np.errstate(all="ignore"):
+        want = f.astype(np.float16).view(np.uint16)
+    got = half(f).reshape(-1)
+    ok = ~np.isnan(f)
+    assert np.array_equal(got[ok], want[ok]) and np.all(np.isnan(got[~ok].view(np.float16)))
+    # progressive buffers: xyz / w, alpha 1
+    assert half([3.0, 6.0, 1.5, 3.0], 1).reshape(-1).tolist() == [0x3C00, 0x4000, 0x3800, 0x3C00]
