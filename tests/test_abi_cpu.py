@@ -27,6 +27,20 @@ def test_every_declared_symbol_is_exported():
     assert L.lib.rtAbiVersion() == 1
 
 
+def test_python_constants_mirror_the_header_enums():
+    """Every RT_INDEX_*, RT_FORMAT_* and RT_VARIANT_* enumerator of include/rtcuda.h has the same value in _lib.py."""
+    hdr = open(os.path.join(ROOT, "include", "rtcuda.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    enums = dict(re.findall(r"\bRT_((?:INDEX|FORMAT|VARIANT)_[A-Z0-9_]+)\s*=\s*(0x[0-9a-fA-F]+|\d+)", hdr))
+    assert len(enums) >= 25
+    for name, value in enums.items():
+        if name == "INDEX_COUNT":
+            continue
+        assert getattr(L, name) == int(value, 0), name
+    mine = {n for n in dir(L) if n.startswith(("INDEX_", "FORMAT_", "VARIANT_"))}
+    assert mine <= set(enums), mine - set(enums)
+
+
 def test_struct_sizes_match_header():
     assert C.sizeof(L.RTLaunchParams) == 64 and C.sizeof(O.RTLaunchParams) == 64
     assert C.sizeof(L.RTDeviceInfo) == 128 + 6 * 4 + 8
