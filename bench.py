@@ -323,6 +323,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     if a.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1 to its workers when the caller set nothing; the CPU arm is to use all the
+        # host's threads (rank 0 alone works), so undo that before libgomp reads it
+        if "TORCHELASTIC_RUN_ID" in os.environ and os.environ.get("OMP_NUM_THREADS") == "1":
+            os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)))
         run_reference(a, rank)
         return
     if world > 1:
