@@ -56,3 +56,48 @@ def test_culling_never_changes_a_query_other_scenes():
         assert int(grp[2]) == 1 and int(grp[0]) == (4 if mode == "floating" else 3)
         r = O.cullcheck(sc, W, H, spp, bounces=4)
         assert r["queries"] > 300_000 and r["mismatches"] == 0, (mode, r["mismatches"])
+
+
+def _box(f, t0, centre, half, yaw, tilt):
+    """12 triangles from t0 on: a box of half extents `half`, turned by `yaw` about y and `tilt` about x.  The eight
+    corners are computed once, so neighbouring faces share them bit for bit (one object group); every face is a quad
+    cut as (v0,v1,v2), (v0,v2,v3), the way scene.swift cuts them."""
+    cy, sy, ct, st = np.cos(yaw), np.sin(yaw), np.cos(tilt), np.sin(tilt)
+    R = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]]) @ np.array([[1, 0, 0], [0, ct, -st], [0, st, ct]])
+    corner = {}
+    for i in (-1, 1):
+        for j in (-1, 1):
+            for k in (-1, 1):
+                corner[(i, j, k)] = (np.asarray(centre) + R @ (np.array([i, j, k]) * half)).astype(np.float32)
+    faces = [[(-1, -1, -1), (-1, -1, 1), (-1, 1, 1), (-1, 1, -1)], [(1, -1, -1), (1, 1, -1), (1, 1, 1), (1, -1, 1)],
+             [(-1, -1, -1), (1, -1, -1), (1, -1, 1), (-1, -1, 1)], [(-1, 1, -1), (-1, 1, 1), (1, 1, 1), (1, 1, -1)],
+             [(-1, -1, -1), (-1, 1, -1), (1, 1, -1), (1, -1, -1)], [(-1, -1, 1), (1, -1, 1), (1, 1, 1), (-1, 1, 1)]]
+    for q, (a, b, c, d) in enumerate(faces):
+        for k, p in enumerate((a, b, c, a, c, d)):
+            o = (3 * (t0 + 2 * q) + k) * 4
+            f[o:o + 3] = corner[p]
+
+
+def test_culling_never_changes_a_query_random_boxes():
+    """Seeded fuzz (24 scenes): the two boxes of the Cornell scene replaced by boxes of random size, place, yaw and tilt (some poke
+    through a wall, some cut each other, some are slivers), seen by a camera inside the room, four bounces: every
+    query of every frame gives the full loop's answer."""
+    W, H, spp = 120, 90, 4
+    g = np.random.default_rng(11)
+    total = 0
+    for scene in range(24):
+        sc = O.cornell(W, H)
+        f = sc["vertices"].view(np.float32)
+        for t0 in (10, 22):
+            half = g.uniform(0.05, 1.1, 3) * (g.random(3) < 0.8) + 0.02
+            _box(f, t0, g.uniform(-2.3, 2.3, 3), half, g.uniform(0, np.pi), g.uniform(-0.6, 0.6) * (scene % 2))
+        cam = sc["camera"].view(np.float32)
+        cam[0:3] = g.uniform(-1.5, 1.5, 3) + (0, 0, 1.0)
+        cam[4:7] = g.uniform(-0.4, 0.4, 3) + (0, 0, -1.0)
+        cam[14] = g.uniform(0.8, 1.6)
+        grp = O.groups(sc)
+        assert int(grp[2]) == 1 and 1 <= int(grp[0]) <= 3, (scene, grp[:4])
+        r = O.cullcheck(sc, W, H, spp, bounces=4)
+        assert r["mismatches"] == 0, (scene, r["mismatches"])
+        total += r["queries"]
+    assert total > 2_500_000
