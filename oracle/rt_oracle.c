@@ -355,6 +355,29 @@ int rt_oracle_intersect(const simd_float3 *vertices, uint32_t numTriangles,
     return h.hit;
 }
 
+/* The closest hit over the triangles ids[0..n) met IN THAT ORDER, chosen by the order-independent form of the
+ * loop's rule that the BVH kernel uses (gpuraytracer_b200/csrc/bvh.cuh, bvh_leaf_closest): smaller cross-multiplied
+ * distance, and on exact equality of the two products the lower primitive id.  Test hook: tests/test_bvh_cpu.py
+ * checks that every order gives rt_oracle_intersect's answer (the ascending strict-less loop). */
+int rt_oracle_intersect_ordered(const simd_float3 *vertices, const uint32_t *ids, uint32_t n,
+                                const float o[3], const float d[3], float tmin, float tmax,
+                                float *distance, uint32_t *primitive_id) {
+    const float *vs = (const float *)vertices;
+    float bestN = tmax, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+    for (uint32_t k = 0; k < n; k++) {
+        const uint32_t id = ids[k];
+        const float *v = vs + (size_t)id * 12;
+        float N = tmax, a = 1.0f;
+        if (!rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &N, &a)) continue;      /* valid and nearer than tmax: (N, a) */
+        const float p1 = N * bestD, p2 = bestN * a;
+        if (p1 < p2 || (p1 == p2 && id < best && best != 0xffffffffu)) { bestN = N; bestD = a; best = id; }
+    }
+    if (distance) *distance = bestN / bestD;
+    if (primitive_id) *primitive_id = best;
+    return best != 0xffffffffu;
+}
+
 /* RTrace/image.swift:40-65.  pow() is the one place the host image writer uses
  * libm; the GPU resolve kernel is checked against this with +-1 LSB. */
 void rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels) {

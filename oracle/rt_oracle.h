@@ -68,6 +68,9 @@ int      rt_oracle_intersect(const simd_float3 *vertices, uint32_t numTriangles,
                              const SphereGPU *spheres, uint32_t numSpheres,
                              const float o[3], const float d[3], float tmin, float tmax,
                              int acceptAny, float *distance, uint32_t *primitive_id);
+int      rt_oracle_intersect_ordered(const simd_float3 *vertices, const uint32_t *ids, uint32_t n,
+                                     const float o[3], const float d[3], float tmin, float tmax,
+                                     float *distance, uint32_t *primitive_id);   /* bvh.cuh's order-independent rule */
 /* image.swift:40-65: x2 exposure, Reinhard, gamma 2.2 -> RGBA8 */
 void     rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels);
 void     rt_oracle_resolve_rgba16f(const float *rgba, uint16_t *out, uint64_t npixels, int divide_by_alpha);

@@ -137,3 +137,52 @@ def test_no_ray_loses_its_hit_to_a_box():
             assert np.all(tn <= np.float32(dist.value) * np.float32(1.00005)), (n, k, o, d, pid.value, tn.max(), dist.value)
             checked += 1
     assert checked > 3000
+
+
+def test_closest_hit_does_not_depend_on_the_order_triangles_are_met_in():
+    """The BVH kernel meets the triangles in tree order and picks the closest by "smaller cross-multiplied distance, on
+    an exact tie the lower id" (oracle hook rt_oracle_intersect_ordered = csrc/bvh.cuh bvh_leaf_closest).  That must be
+    the ascending strict-less loop's answer (rt_oracle_intersect) whatever the order -- checked on rays made to tie:
+    axis-parallel rays through the grid vertices and edges of tessellated walls (up to six triangles share the hit
+    point, distance bit-equal), rays through vertices from random origins, and plain random rays."""
+    sc = O.cornell(64, 64)
+    g = np.random.default_rng(9)
+    O.lib.rt_oracle_intersect_ordered.restype = C.c_int
+    d0, p0, d1, p1 = C.c_float(), C.c_uint32(), C.c_float(), C.c_uint32()
+    ties = 0
+    for n in (1, 4, 8):
+        verts, T = (sc["vertices"], 36) if n == 1 else tessellate(sc["vertices"], sc["materials"], 36, n)[::2]
+        v = verts.view(np.float32).reshape(T, 3, 4)[:, :, :3]
+        for k in range(400):
+            t = int(g.integers(T)); corner = v[t, int(g.integers(3))]
+            kind = k % 4
+            if kind == 0:                                   # axis-parallel through a vertex
+                a = int(g.integers(3)); o = corner.copy(); o[a] = np.float32(g.uniform(-2.0, 2.0))
+                d = np.zeros(3, np.float32); d[a] = np.sign(corner[a] - o[a]) or 1.0
+            elif kind == 1:                                 # axis-parallel through an edge midpoint
+                mid = ((corner + v[t, int(g.integers(3))]) * np.float32(0.5)).astype(np.float32)
+                a = int(g.integers(3)); o = mid.copy(); o[a] = np.float32(g.uniform(-2.0, 2.0))
+                d = np.zeros(3, np.float32); d[a] = np.sign(mid[a] - o[a]) or 1.0
+            elif kind == 2:                                 # towards a vertex from anywhere
+                o = g.uniform(-2.4, 2.4, 3).astype(np.float32)
+                d = (corner - o).astype(np.float32); d = (d / np.float32(np.linalg.norm(d))).astype(np.float32)
+            else:
+                o = g.uniform(-2.4, 2.4, 3).astype(np.float32)
+                d = g.normal(size=3); d = (d / np.linalg.norm(d)).astype(np.float32)
+            hit = O.lib.rt_oracle_intersect(O.vp(verts), T, None, 0, O.vp(o), O.vp(d), C.c_float(1e-3), C.c_float(1000.0),
+                                            0, C.byref(d0), C.byref(p0))
+            for perm in range(6):                           # ascending, descending, four random orders
+                ids = (np.arange(T) if perm == 0 else np.arange(T)[::-1] if perm == 1 else g.permutation(T)).astype(np.uint32)
+                h = O.lib.rt_oracle_intersect_ordered(O.vp(verts), O.vp(np.ascontiguousarray(ids)), T, O.vp(o), O.vp(d),
+                                                      C.c_float(1e-3), C.c_float(1000.0), C.byref(d1), C.byref(p1))
+                assert h == hit, (n, k, perm)
+                if hit:
+                    assert p1.value == p0.value and np.float32(d1.value).view(np.uint32) == np.float32(d0.value).view(np.uint32), \
+                        (n, k, perm, p0.value, p1.value, d0.value, d1.value)
+            if hit and kind < 2:
+                # was there a tie to break?  (the next triangle alone gives the same distance: the other half of a quad)
+                one = np.array([p0.value + 1], np.uint32)
+                if p0.value + 1 < T and O.lib.rt_oracle_intersect_ordered(O.vp(verts), O.vp(one), 1, O.vp(o), O.vp(d), C.c_float(1e-3),
+                                                                         C.c_float(1000.0), C.byref(d1), C.byref(p1)):
+                    ties += int(np.float32(d1.value) == np.float32(d0.value))
+    assert ties > 50
