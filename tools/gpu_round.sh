@@ -13,6 +13,7 @@ timeout 300 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; tail -2 
 timeout 600 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench exit $?"; cat $O/${TAG}_bench.json
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_reference.json 2>> $O/${TAG}_bench.err; cat $O/${TAG}_bench_reference.json
 timeout 300 python tools/time_variants.py 1920 1080 64 1,2 > $O/${TAG}_variants.log 2>&1; cat $O/${TAG}_variants.log
+timeout 120 python tools/time_bvh.py > $O/${TAG}_bvh_timing.txt 2>&1; tail -5 $O/${TAG}_bvh_timing.txt
 # ncu pass 1: launch list of the bench command (shares, not absolutes)
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 timeout 300 $CMD > $O/${TAG}_plain.log 2>&1 &&
