@@ -93,11 +93,17 @@ class ClockSampler:
         rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 7] or [r for _, r in self.rows[-3:] if len(r) >= 7]
         if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(r[0]) for r in rows)
+        def num(x):                                        # "[N/A]" on a field must not take the bench down
+            try:
+                return float(x)
+            except ValueError:
+                return None
+        sm = sorted(v for v in (num(r[0]) for r in rows) if v is not None)
+        power = [v for v in (num(r[2]) for r in rows) if v is not None]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]),
-                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows), "reasons": reasons}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": num(rows[0][1]),
+                "power_w_max": max(power) if power else None, "samples": len(rows), "reasons": reasons}
 
 
 # --------------------------------------------------------------- cpu oracle ----
