@@ -77,3 +77,55 @@ def test_the_rule_never_drops_the_triangle_a_camera_ray_hits():
                     assert keep[pid.value], (scene, tile, px, py, jx, jy, pid.value)
                     checked += 1
     assert checked > 15_000 and dropped_some > 1_000       # the rule does drop things: the check is not vacuous
+
+
+def kept_sphere(cf, centre, r, x0, x1, y0, y1):
+    """camera_candidates, sphere part: the box bound of x/z and y/z over the sphere's bounding cube"""
+    q = (centre - cf["o"]).astype(f32)
+    zc = -(q @ cf["w"]); xc = q @ cf["u"]; yc = q @ cf["v"]
+    far = np.sqrt(q @ q)
+    safe = zc - r > 0.01 * (far + r) and r > 1e-3 * far
+    zn, zf = zc - r, zc + r
+    with np.errstate(all="ignore"):
+        txh = (xc + r) / (zn if xc + r >= 0 else zf); txl = (xc - r) / (zn if xc - r <= 0 else zf)
+        tyh = (yc + r) / (zn if yc + r >= 0 else zf); tyl = (yc - r) / (zn if yc - r <= 0 else zf)
+        Xh = (txh / cf["half_w"] + 1.0) * (0.5 * cf["res_x"]); Xl = (txl / cf["half_w"] + 1.0) * (0.5 * cf["res_x"])
+        Yl = (1.0 - tyh / cf["half_h"]) * (0.5 * cf["res_y"]); Yh = (1.0 - tyl / cf["half_h"]) * (0.5 * cf["res_y"])
+    outside = Xh < x0 - 1.0 or Xl > x1 + 2.0 or Yh < y0 - 1.0 or Yl > y1 + 2.0
+    return not (safe and outside)
+
+
+def test_the_rule_never_drops_the_sphere_a_camera_ray_hits():
+    """Config 4's scene (256 spheres, 8 light triangles), cameras between the spheres and outside the room."""
+    W, H = 160, 120
+    g = np.random.default_rng(22)
+    o = np.zeros(3, f32); d = np.zeros(3, f32)
+    dist = C.c_float(); pid = C.c_uint32()
+    checked = dropped = 0
+    for scene in range(16):
+        sc = O.spheres(W, H)
+        T, S = sc["T"], sc["S"]
+        cam = sc["camera"]; c = cam.view(f32)
+        if scene % 2:
+            c[0:3] = g.uniform(-2.2, 2.2, 3); c[4:7] = g.normal(size=3)
+        else:
+            c[0:3] = g.uniform(-1.0, 1.0, 3) + (0, 0, g.uniform(4.0, 10.0)); c[4:7] = g.uniform(-0.3, 0.3, 3) + (0, 0, -1.0)
+        c[14] = g.uniform(0.3, 2.0)
+        cf = camera_frame(cam)
+        sp = sc["spheres"].view(f32).reshape(S, 20)
+        v = sc["vertices"].view(f32).reshape(T, 3, 4)[:, :, :3]
+        for tile in range(20):
+            x0 = int(g.integers(0, W // 8)) * 8; y0 = int(g.integers(0, H // 4)) * 4
+            keep = [kept(cf, v[t], x0, x0 + 7, y0, y0 + 3) for t in range(T)] + \
+                   [kept_sphere(cf, sp[s, 0:3], abs(sp[s, 16]), x0, x0 + 7, y0, y0 + 3) for s in range(S)]
+            dropped += len(keep) - sum(keep)
+            for ray in range(16):
+                jx, jy = f32(g.random()), f32(g.random())
+                px = x0 + (int(g.choice((0, 7))) if ray < 8 else int(g.integers(8)))
+                py = y0 + (int(g.choice((0, 3))) if ray < 8 else int(g.integers(4)))
+                O.lib.rt_oracle_camera_ray(O.vp(cam), px, py, C.c_float(jx), C.c_float(jy), O.vp(o), O.vp(d))
+                if O.lib.rt_oracle_intersect(O.vp(sc["vertices"]), T, O.vp(sc["spheres"]), S, O.vp(o), O.vp(d), C.c_float(1e-3),
+                                             C.c_float(1000.0), 0, C.byref(dist), C.byref(pid)):
+                    assert keep[pid.value], (scene, tile, px, py, pid.value)
+                    checked += 1
+    assert checked > 2_000 and dropped > 40_000
