@@ -4,6 +4,8 @@ at build time).  Run from the repo root:  python tests/golden/make_golden.py
 Outputs (float32 / uint32, bit-exact expectations):
   pathtrace_cornell_64x48_ref400spp.npz   image of the reference kernel at its literals
                                           (400 spp, 3 bounces), offsets seed 3, + the inputs
+  pathtrace_cornell_80x60_moved_ref400spp.npz   the same kernel seen by a camera inside the room: off-axis direction,
+                                          rolled up vector, 100 degrees wide; offsets seed 5
   drawtriangle_cornell_64x48_ref.npz      RGBA8 + float3 buffers of the reference MIS kernel (6 x 300)
   halton_ref.npz                          halton(i, d) of sampling.metal:107-122 for 4096 (i, d)
 """
@@ -25,6 +27,15 @@ off = O.offsets(W, 0, H, seed=3)
 img = R.pathtrace(ref, sc, W, H, off)
 np.savez_compressed(os.path.join(HERE, "pathtrace_cornell_64x48_ref400spp.npz"), image=img, offsets=off,
                     camera=sc["camera"], materials=sc["materials"], lights=sc["lights"], vertices=sc["vertices"])
+# a second camera: inside the room, looking down and to the left, rolled, wide
+W2, H2 = 80, 60
+sc2 = O.cornell(W2, H2)
+cam = sc2["camera"].view(np.float32)
+cam[0:3] = (0.8, 0.6, 2.1); cam[4:7] = (-0.45, -0.35, -1.0); cam[8:11] = (0.15, 1.0, 0.05); cam[14] = 1.75
+off2 = O.offsets(W2, 0, H2, seed=5)
+img2 = R.pathtrace(ref, sc2, W2, H2, off2)
+np.savez_compressed(os.path.join(HERE, "pathtrace_cornell_80x60_moved_ref400spp.npz"), image=img2, offsets=off2,
+                    camera=sc2["camera"], materials=sc2["materials"], lights=sc2["lights"], vertices=sc2["vertices"])
 # mode B: the reference MIS kernel at its literals (6 camera rays, 300 MIS samples), 1.5 x 1.5 light
 scb = O.cornell(W, H, light_size=1.5)
 pxb, txb = R.drawtriangle(ref, scb, W, H)

@@ -30,6 +30,17 @@ def test_oracle_pathtrace_matches_golden_image():
     assert np.array_equal(got.view(np.uint32), g["image"].view(np.uint32))
 
 
+def test_oracle_pathtrace_matches_golden_image_moved_camera():
+    """The reference kernel seen from inside the room (off-axis, rolled, 100 degrees wide): 80 x 60 at its literals."""
+    g = golden("pathtrace_cornell_80x60_moved_ref400spp.npz")
+    sc = O.cornell(80, 60)
+    for k in ("materials", "lights", "vertices"):
+        assert np.array_equal(sc[k], g[k]), k
+    sc["camera"] = g["camera"].copy()
+    got, _ = O.pathtrace(sc, 80, 60, 400, bounces=3, off=g["offsets"].copy())
+    assert np.array_equal(got.view(np.uint32), g["image"].view(np.uint32))
+
+
 def test_oracle_drawtriangle_matches_golden():
     g = golden("drawtriangle_cornell_64x48_ref.npz")
     sc = O.cornell(64, 48, light_size=1.5)
@@ -46,6 +57,17 @@ def test_gpu_pathtrace_matches_golden_image():
     g = golden("pathtrace_cornell_64x48_ref400spp.npz")
     r = G.Renderer(G.init_cornell_box(64, 48), 64, 48, offsets=g["offsets"].copy())
     img = r.draw()                                        # no overrides: the shader's own 400 spp / 3 bounces
+    assert np.array_equal(img.view(np.uint32), g["image"].view(np.uint32)), f"{(img != g['image']).sum()} values differ"
+
+
+@pytest.mark.gpu
+def test_gpu_pathtrace_matches_golden_image_moved_camera():
+    import gpuraytracer_b200 as G
+    g = golden("pathtrace_cornell_80x60_moved_ref400spp.npz")
+    scene = G.init_cornell_box(80, 60)
+    scene.camera.view(np.uint8)[:] = g["camera"].view(np.uint8)
+    r = G.Renderer(scene, 80, 60, offsets=g["offsets"].copy())
+    img = r.draw()
     assert np.array_equal(img.view(np.uint32), g["image"].view(np.uint32)), f"{(img != g['image']).sum()} values differ"
 
 
