@@ -7,7 +7,7 @@ import subprocess
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
+_PATH = os.environ.get("ORACLE_LIB") or os.path.join(ROOT, "oracle", "liboracle.so")   # (override: the sanitizer build, oracle/Makefile)
 if not os.path.exists(_PATH):
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
 lib = C.CDLL(_PATH)
