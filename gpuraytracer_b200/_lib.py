@@ -19,7 +19,7 @@ lib = C.CDLL(LIB_PATH)
 
 RT_OK = 0
 RT_ERR = {-1: "INVALID_ARGUMENT", -2: "UNKNOWN_KERNEL", -3: "NO_DRIVER", -4: "MISSING_BINDING",
-          -5: "OUT_OF_RANGE", -6: "STATE", -7: "UNSUPPORTED", -8: "OUT_OF_MEMORY"}
+          -5: "OUT_OF_RANGE", -6: "STATE", -7: "UNSUPPORTED", -8: "OUT_OF_MEMORY", -9: "DEVICE_TIMEOUT"}
 
 INDEX_CAMERA, INDEX_MATERIALS, INDEX_LIGHTS, INDEX_VERTICES, INDEX_PIXELS = 0, 1, 2, 3, 4
 INDEX_ACCEL, INDEX_DEBUG, INDEX_SPHERES, INDEX_OUTPUT, INDEX_OFFSETS = 5, 6, 7, 16, 17

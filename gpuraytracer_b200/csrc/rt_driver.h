@@ -19,7 +19,7 @@
     X(cuDeviceGetAttribute) X(cuDeviceTotalMem) X(cuDevicePrimaryCtxRetain) \
     X(cuDevicePrimaryCtxRelease) X(cuCtxSetCurrent) X(cuModuleLoadData) X(cuModuleUnload) \
     X(cuModuleGetFunction) X(cuModuleGetGlobal) X(cuFuncSetAttribute) X(cuMemAlloc) X(cuMemFree) \
-    X(cuMemHostAlloc) X(cuMemFreeHost) X(cuMemcpyHtoD) X(cuMemcpyDtoH) X(cuMemcpyHtoDAsync) \
+    X(cuMemHostAlloc) X(cuMemHostGetDevicePointer) X(cuMemFreeHost) X(cuMemcpyHtoD) X(cuMemcpyDtoH) X(cuMemcpyHtoDAsync) \
     X(cuMemcpyDtoHAsync) X(cuMemcpyDtoDAsync) X(cuMemsetD8) X(cuMemsetD8Async) X(cuStreamCreate) \
     X(cuStreamDestroy) X(cuStreamSynchronize) X(cuEventCreate) X(cuEventRecord) \
     X(cuEventSynchronize) X(cuEventElapsedTime) X(cuEventDestroy) X(cuLaunchKernel) \

@@ -221,7 +221,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
     if (lane < RT_SORT_KEYS) cnts[lane] = 0u;
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (PERSIST && chunk > 0) {
-        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
+        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns, ts.status);
         lum = mk(o.x, o.y, o.z);
     } else if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
     __syncwarp();

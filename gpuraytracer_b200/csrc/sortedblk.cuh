@@ -127,7 +127,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (SPATIAL) {
     } else if (PERSIST && chunk > 0) {
-        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
+        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns, ts.status);
         lum = mk(o.x, o.y, o.z);
     } else if (p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 

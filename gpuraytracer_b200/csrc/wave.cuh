@@ -41,14 +41,41 @@
 struct RTTileSched {
     unsigned int *counter;     /* next unit; zeroed by rt_prep_scene (prepared-scene header) */
     unsigned int *flags;       /* per warp tile (4 per block tile): chunks completed; zeroed by the host before the launch */
+    unsigned int *status;      /* host-mapped word of the queue: a bit is set when a wait below gives up (rtcuda.cpp turns it
+                                  into RT_ERR_DEVICE_TIMEOUT at rtWaitUntilCompleted); never written otherwise */
     uint32_t chunks, chunkSpp;
 };
+#define RT_STATUS_CHUNK_WAIT_TIMEOUT 1u
+/* how long a warp waits for the chunk before its own, in ns of %globaltimer.  The producer holds a smaller ticket, so
+ * it is running or done and the legitimate wait is at most one unit's run time (milliseconds; under
+ * compute-sanitizer hundreds of them): the bound only exists so that a lost flag write or a corrupt flag array
+ * ends as an error code instead of a hung GPU, like the bounded BVH walk (bvh.cuh). */
+#define RT_CHUNK_WAIT_NS 8000000000ull
 
 /* the two rare steps of a chunked unit, out of line so that they do not disturb the register allocation of the loops */
-__device__ __noinline__ float4 tiles_wait_for_previous_chunk(const unsigned int *flag, uint32_t chunk, const float4 *src, bool owns) {
+__device__ __forceinline__ unsigned long long rt_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ float4 tiles_wait_for_previous_chunk(const unsigned int *flag, uint32_t chunk, const float4 *src, bool owns,
+                                                             unsigned int *status) {
     if ((threadIdx.x & 31) == 0) {
         unsigned int done;
-        do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(flag) : "memory"); } while (done < chunk);
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(flag) : "memory");
+        if (done < chunk) {
+            const unsigned long long t0 = rt_globaltimer();
+            uint32_t spins = 0;
+            do {
+                __nanosleep(64);
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(flag) : "memory");
+                /* the clock is read every 256th poll only */
+                if (done < chunk && (++spins & 255u) == 0u && rt_globaltimer() - t0 > RT_CHUNK_WAIT_NS) {
+                    atomicOr_system(status, RT_STATUS_CHUNK_WAIT_TIMEOUT);
+                    break;
+                }
+            } while (done < chunk);
+        }
     }
     __syncwarp();
     return owns ? __ldcg(src) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -160,7 +187,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     f3 lum = mk(0.0f, 0.0f, 0.0f);
     if (PERSIST && chunk > 0) {
         /* the running sum of the samples before kBegin, once the block that made it has published it */
-        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns);
+        const float4 o = tiles_wait_for_previous_chunk(ts.flags + tile, chunk, out + pix, owns, ts.status);
         lum = mk(o.x, o.y, o.z);
     } else if (!SPATIAL && p.accumulate && owns) { float4 o = out[pix]; lum = mk(o.x, o.y, o.z); }
 

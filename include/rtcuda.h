@@ -44,7 +44,8 @@ enum {
     RT_ERR_OUT_OF_RANGE     = -5,   /* binding too small for the launch           */
     RT_ERR_STATE            = -6,   /* call order (e.g. wait before commit)       */
     RT_ERR_UNSUPPORTED      = -7,   /* e.g. bounces > 4 (primes[24] would overrun) */
-    RT_ERR_OUT_OF_MEMORY    = -8
+    RT_ERR_OUT_OF_MEMORY    = -8,
+    RT_ERR_DEVICE_TIMEOUT   = -9    /* a kernel gave up a bounded wait (chunk hand-over of the ticketed forms): the image is invalid */
 };
 
 typedef struct RTDevice   RTDevice;    /* MTLDevice                                   */

@@ -11,6 +11,9 @@ W, H = 72, 44                    # ragged against the 16 x 8 block and the 8 x 4
 dev = G.Device(0)
 r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
 first = None
+# the ticketed forms cut the samples into chunks only on large launches: force three (6 + 6 + 1 samples) so that
+# the chunk hand-over across blocks (wave.cuh: tiles_wait_for_previous_chunk / tiles_publish_chunk) runs here
+os.environ["RT_TILES_CHUNKS"] = "3"
 for name in ("DEFAULT", "SMEM", "CONST", "WAVE", "TILES", "SORTED", "SORTED_TILES", "SORTED_BLOCK", "SORTED_BLOCK_TILES", "BVH"):
     img = r.draw(spp=13, variant=getattr(L, "VARIANT_" + name))
     first = img if first is None else first
@@ -26,3 +29,5 @@ tv, tm, T = tessellate(sc.vertices, sc.materials, 36, 6)
 sc.vertices, sc.materials, sc.num_triangles = tv, tm, T
 print("bvh, 1296 triangles    mean", float(G.Renderer(sc, W, H, device=dev).draw(spp=3)[..., :3].mean()), flush=True)
 print("rgba8 / rgba16f resolve", r.resolve_rgba8().shape, r.resolve_rgba16f().shape, flush=True)
+px, text = G.draw_triangle(G.init_cornell_box(W, H, light_size=1.5), W, H, device=dev, camera_rays=2, mis_samples=30)
+print("drawTriangle_mis       mean", float(text.mean()), px.shape, flush=True)
