@@ -159,7 +159,7 @@ struct RTBvhArgs { const float4 *nodes; const float4 *tris; uint32_t numNodes, p
  * registers, 64 bytes of spills) another +3 % (profiles/r03g_bvh_forms.txt). */
 __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                    float4 *__restrict__ out, const RTLaunchParams &p, const RTSceneLayout &lay,
-                                                   const RTBvhArgs &ba, float *sm) {
+                                                   const RTBvhArgs &ba, float *sm, const RTHaltonTables &ht) {
     for (uint32_t k = threadIdx.x; k < RT_HDR_WORDS; k += RT_BLOCK_THREADS) sm[k] = scene[k];
     for (uint32_t k = threadIdx.x; k < RT_LIGHT_WORDS * lay.L; k += RT_BLOCK_THREADS) sm[RT_HDR_WORDS + k] = scene[lay.light + k];
     __syncthreads();
@@ -192,7 +192,7 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
 #pragma unroll 1
     for (uint32_t k = 0; k < p.spp; k++) {
         const uint32_t i = offset + (p.firstSample + k);
-        float jx = halton<0>(i), jy = halton<1>(i);                     /* sampling.metal:141-147 */
+        float jx = halton<0>(i), jy = halton_cam_y(ht, i);              /* sampling.metal:141-147 */
         float s = ((fx + jx) / resX) * 2.0f - 1.0f;
         float t = -(((fy + jy) / resY) * 2.0f - 1.0f);
         f3 rd = normalize((cam_u * (s * halfW) + cam_v * (t * halfH)) - cam_w);
@@ -210,7 +210,8 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
             const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
             const f3 diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
             f3 P = (ro + rd * dist) + normal * 1e-3f;                   /* :67 */
-            float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b); /* :72-73 */
+            const float4 h4 = halton_bounce4(ht, i, b);                 /* the bounce's four Halton values (RTHaltonTables) */
+            const float wx = h4.x, wy = h4.y;                           /* :72-73 */
             color = color * diffuse;                                    /* :76 */
             for (uint32_t l = 0; l < numLights; l++) {
                 const float *L = lights + RT_LIGHT_WORDS * l;
@@ -222,7 +223,7 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
             if (b + 1 >= nb) break;
             const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
             const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
-            float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b); /* :93-94 */
+            const float ux = h4.z, uy = h4.w;                           /* :93-94 */
             f3 sdir = sample_cosine_hemisphere(ux, uy);
             rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;     /* sampling.metal:65 */
             ro = P;                                                     /* :99-100 */
@@ -239,9 +240,9 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
 #define RT_BVH_ENTRY(name, MINB)                                                                                 \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
-         const RTLaunchParams p, const RTSceneLayout lay, const RTBvhArgs ba) {                                  \
+         const RTLaunchParams p, const RTSceneLayout lay, const RTBvhArgs ba, const RTHaltonTables ht) {         \
         extern __shared__ __align__(16) float sm[];          /* header, then the lights */                       \
-        pathtrace_bvh_body(scene, offsets, out, p, lay, ba, sm);                                                 \
+        pathtrace_bvh_body(scene, offsets, out, p, lay, ba, sm, ht);                                             \
     }
 RT_BVH_ENTRY(pathTrace_bvh, 8)
 #ifdef RT_TUNING_VARIANTS   /* RT_BVH_FORM=<suffix> (rtcuda.cpp), tools/time_bvh.py: blocks per SM */

@@ -149,7 +149,27 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
             always |= pairs;
         }
     }
-    if (lane == 0) { gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; }
+    /* the shell: always-tested quads in a face plane of the always-tested quads' own bounds (rt_scene_layout.h) */
+    const bool mine = has && ((always >> lane) & 1u);
+    float alo[3], ahi[3];
+    bool face = false;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        alo[k] = warp_min(mine ? lo[k] : INF); ahi[k] = warp_max(mine ? hi[k] : -INF);
+        face = face || (mine && lo[k] == hi[k] && (lo[k] == alo[k] || lo[k] == ahi[k]));
+    }
+    const uint32_t shell = __ballot_sync(0xffffffffu, face);
+    if (lane == 0) {
+        float *r = gf + RT_GRP_SHELL_BOX;
+        const float shrink = ext * (1.0f / 16384.0f);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            r[k] = shell ? (alo[k] + ahi[k]) * 0.5f : 0.0f;
+            r[4 + k] = shell ? (ahi[k] - alo[k]) * 0.5f - shrink : 0.0f;
+        }
+        r[3] = 0.0f; r[7] = 0.0f;
+        gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; gu[RT_GRP_SHELL] = shell;
+    }
 }
 
 extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camera,
@@ -981,18 +1001,19 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
 #define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB, SPATIAL)                                                            \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
-         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTHaltonTables ht) {                                                                              \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_wave_body<COUNT, UNROLL, R, false, SPATIAL>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
+        pathtrace_wave_body<COUNT, UNROLL, R, false, SPATIAL>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
     }
 /* ticketed form: one block per (tile, sample chunk) unit, named by a ticket from an atomic counter (wave.cuh: RTTileSched) */
 #define RT_WAVE_PERSIST_ENTRY(name, COUNT, UNROLL, R, MINB)                                                      \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
-         const RTTileSched ts) {                                                                                 \
+         const RTHaltonTables ht, const RTTileSched ts) {                                                        \
         extern __shared__ __align__(16) float sm[];                                                              \
-        pathtrace_wave_body<COUNT, UNROLL, R, true, false>(scene, offsets, out, p, lay, sm, counters, ts);       \
+        pathtrace_wave_body<COUNT, UNROLL, R, true, false>(scene, offsets, out, p, lay, sm, counters, ts, ht);   \
     }
 /* warp-level path compaction, R samples per pixel per round; rtcuda.cpp adds the queue memory.
  * R = 6 with four blocks per SM is the default (46 KB of queues per block): measured 5 615 Mpaths/s against
@@ -1025,23 +1046,24 @@ RT_WAVE_ENTRY(pathTrace_exp12, false, 4, 12, 2, false)
 #define RT_SORTED_ENTRY(name, R, MINB)                                                                           \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
-         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTHaltonTables ht) {                                                                              \
         extern __shared__ __align__(16) float sm[];                                                              \
         if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
-            pathtrace_sorted_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{});                     \
+            pathtrace_sorted_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{}, ht);                 \
         else                                                                                                     \
-            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
+            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
     }
 #define RT_SORTED_PERSIST_ENTRY(name, R, MINB)                                                                   \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
-         const RTTileSched ts) {                                                                                 \
+         const RTHaltonTables ht, const RTTileSched ts) {                                                        \
         extern __shared__ __align__(16) float sm[];                                                              \
         if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
-            pathtrace_sorted_body<R, true>(scene, offsets, out, p, lay, sm, ts);                                 \
+            pathtrace_sorted_body<R, true>(scene, offsets, out, p, lay, sm, ts, ht);                             \
         else                                                                                                     \
-            pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);        \
+            pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts, ht);    \
     }
 /* 15 words per slot: R = 6 fits four blocks per SM beside the Cornell scene (53 KB per block) */
 RT_SORTED_ENTRY(pathTrace_sorted4, 4, 4)
@@ -1056,23 +1078,25 @@ RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
 #define RT_SORTEDBLK_ENTRY(name, R, MINB)                                                                        \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
-         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {           \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTHaltonTables ht) {                                                                              \
         extern __shared__ __align__(16) float sm[];                                                              \
         if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
-            pathtrace_sortedblk_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{});                  \
+            pathtrace_sortedblk_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{}, ht);              \
         else                                                                                                     \
-            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}); \
+            pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
     }
 RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)
 /* fewer samples per launch than a round has slots (progressive rendering): G = 6 / spp tiles side by side per warp */
 extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
 pathTrace_sortedblk_wide6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
-                          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {
+                          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,
+                          const RTHaltonTables ht) {
     extern __shared__ __align__(16) float sm[];
     if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])
-        pathtrace_sortedblk_body<6, false, true>(scene, offsets, out, p, lay, sm, RTTileSched{});
+        pathtrace_sortedblk_body<6, false, true>(scene, offsets, out, p, lay, sm, RTTileSched{}, ht);
     else
-        pathtrace_wave_body<false, 4, 6, false, true>(scene, offsets, out, p, lay, sm, counters, RTTileSched{});
+        pathtrace_wave_body<false, 4, 6, false, true>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht);
 }
 #ifdef RT_TUNING_VARIANTS
 RT_SORTEDBLK_ENTRY(pathTrace_exp14, 4, 5)      /* 512 slots, five blocks per SM */
@@ -1081,17 +1105,28 @@ RT_SORTEDBLK_ENTRY(pathTrace_exp15, 5, 4)
 extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
 pathTrace_sortedblk_tiles6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
                            const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,
-                           const RTTileSched ts) {
+                           const RTHaltonTables ht, const RTTileSched ts) {
     extern __shared__ __align__(16) float sm[];
     if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])
-        pathtrace_sortedblk_body<6, true>(scene, offsets, out, p, lay, sm, ts);
+        pathtrace_sortedblk_body<6, true>(scene, offsets, out, p, lay, sm, ts, ht);
     else
-        pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts);
+        pathtrace_wave_body<false, 4, 4, true, false>(scene, offsets, out, p, lay, sm, counters, ts, ht);
 }
 
 #include "bvh.cuh"
 
 #include "modeb.cuh"
+
+/* --------------------------------------------------------- Halton tables ---- */
+/* rt_device_math.cuh: RTHaltonTables.  bounce[b * n + i] = halton_slot<0..3>(i, b), camY[i] = halton<1>(i): the very
+ * functions the kernels would otherwise call, so a looked-up value is the computed one bit for bit. */
+extern "C" __global__ void rt_build_halton(float4 *__restrict__ bounce, float *__restrict__ camY, uint32_t n, uint32_t bounces) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    camY[i] = halton<1>(i);
+    for (uint32_t b = 0; b < bounces; b++)
+        bounce[(size_t)b * n + i] = make_float4(halton_slot<0>(i, b), halton_slot<1>(i, b), halton_slot<2>(i, b), halton_slot<3>(i, b));
+}
 
 /* ----------------------------------------------------------------- resolve ---- */
 /* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.

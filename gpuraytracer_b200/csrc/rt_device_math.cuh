@@ -236,6 +236,33 @@ __device__ __noinline__ float halton_rt(uint32_t i, uint32_t d) {
     return r;
 }
 
+/* ---- Halton values out of a table in global memory ---------------------------------
+ * halton(i, d) depends on the index and the dimension only, and the indices of a frame all lie in
+ * [0, 2^20 + firstSample + spp) (offsets are arc4random() % 2^20, renderer.swift:100).  The four values of a
+ * bounce (31 digit steps, ~170 instructions, a fifth of the sorted kernel) are therefore looked up: one 16-byte
+ * load per path and bounce from a table of n x bounces float4 (55 MB for three bounces, 3 % of B200's HBM and
+ * within its L2) that rt_build_halton filled with halton_slot<0..3>(i, b) -- the SAME device function, so the
+ * values are the computed ones bit for bit; camY holds halton<1>(i) (14 base-3 digits) for the camera jitter.
+ * An index beyond the table (offsets a caller chose larger) falls back to the computation, out of line.
+ * rtcuda.cpp owns the tables (per device, built on first use, grown on demand). */
+struct RTHaltonTables {
+    const float4 *bounce;      /* [bounces][n] */
+    const float  *camY;        /* [n] */
+    uint32_t n, bounces;
+};
+__device__ __noinline__ float4 halton_bounce4_compute(uint32_t i, uint32_t b) {
+    return make_float4(halton_slot<0>(i, b), halton_slot<1>(i, b), halton_slot<2>(i, b), halton_slot<3>(i, b));
+}
+__device__ __noinline__ float halton_cam_y_compute(uint32_t i) { return halton<1>(i); }
+__device__ __forceinline__ float4 halton_bounce4(const RTHaltonTables &ht, uint32_t i, uint32_t b) {
+    if (i < ht.n && b < ht.bounces) return __ldg(ht.bounce + (size_t)b * ht.n + i);
+    return halton_bounce4_compute(i, b);
+}
+__device__ __forceinline__ float halton_cam_y(const RTHaltonTables &ht, uint32_t i) {
+    if (i < ht.n) return __ldg(ht.camY + i);
+    return halton_cam_y_compute(i);
+}
+
 /* sampling.metal:68-75 */
 __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
     x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;

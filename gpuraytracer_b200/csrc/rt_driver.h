@@ -17,7 +17,7 @@
 #define RT_DRIVER_FUNCTIONS(X) \
     X(cuInit) X(cuGetErrorString) X(cuDeviceGet) X(cuDeviceGetCount) X(cuDeviceGetName) \
     X(cuDeviceGetAttribute) X(cuDeviceTotalMem) X(cuDevicePrimaryCtxRetain) \
-    X(cuDevicePrimaryCtxRelease) X(cuCtxSetCurrent) X(cuModuleLoadData) X(cuModuleUnload) \
+    X(cuDevicePrimaryCtxRelease) X(cuCtxSetCurrent) X(cuCtxSynchronize) X(cuModuleLoadData) X(cuModuleUnload) \
     X(cuModuleGetFunction) X(cuModuleGetGlobal) X(cuFuncSetAttribute) X(cuMemAlloc) X(cuMemFree) \
     X(cuMemHostAlloc) X(cuMemHostGetDevicePointer) X(cuMemFreeHost) X(cuMemcpyHtoD) X(cuMemcpyDtoH) X(cuMemcpyHtoDAsync) \
     X(cuMemcpyDtoHAsync) X(cuMemcpyDtoDAsync) X(cuMemsetD8) X(cuMemsetD8Async) X(cuStreamCreate) \

@@ -28,6 +28,12 @@
  *            then K records of 8 words: box centre xyz, pair mask (uint) | inflated half extent xyz, -
  *            A group is a connected set of quads (connected = some vertex bit-equal), its box the bounds of
  *            its vertices grown by 1/128 of the scene's largest extent.
+ *            [3] the SHELL: those always-tested quads that lie in a face plane of the always-tested quads' own bounds
+ *            (all six vertices bit-equal to the bound on one axis: the walls of a room).  After the K records, 8 words:
+ *            centre xyz of those bounds, - | half extent xyz shrunk by 1/16384 of the scene's largest extent, -.
+ *            A shadow ray whose two ends both lie inside the shrunk box cannot be accepted by a shell quad (the
+ *            segment stays 3e-4 x extent clear of its plane; the test's own error is 1e-6 x extent), so those
+ *            any-hit tests are skipped (sortedblk.cuh / sorted.cuh, pass B).
  */
 #ifndef RT_SCENE_LAYOUT_H
 #define RT_SCENE_LAYOUT_H
@@ -73,10 +79,12 @@
                                  sampleAreaLight uses: 0.25, 0.25 (sampling.metal:207-209) or width/2, depth/2 (RT_LAYOUT_LIGHT_EXTENT) */
 #define RT_LAYOUT_LIGHT_EXTENT 1u
 #define RT_MAX_GROUPS     4   /* cullable object groups (16 sort keys)                                 */
-#define RT_GROUP_WORDS   (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_K          0
 #define RT_GRP_ALWAYS     1
 #define RT_GRP_OK         2
+#define RT_GRP_SHELL      3
+#define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
+#define RT_GROUP_WORDS   (RT_GRP_SHELL_BOX + 8)
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
 #define RT_CONST_SLOTS   3584

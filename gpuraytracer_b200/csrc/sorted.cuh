@@ -37,6 +37,9 @@
  */
 #pragma once
 
+#ifndef RT_EXP_TRACE
+#define RT_EXP_TRACE 1         /* A/B builds (tools/build_exp.sh): 0 separate closest / shadow loops, 1 one masked loop, 2 the r03 dual loop, no shell rule, 3 = 2 with the shell rule on the last bounce */
+#endif
 #define RT_SORT_FIELDS 11      /* X.xyz (hit point, then P)  D.xyz (continuation ray)  colour.xyz  light sample point x, z */
 #define RT_SORT_KEYS   (1 << RT_MAX_GROUPS)
 
@@ -104,6 +107,91 @@ __device__ __forceinline__ bool dual_hit_pairs(const SceneRef<false> &sc, uint32
     return best != 0xffffffffu;
 }
 
+/* dual_hit_pairs with the shadow ray tested against a SUBSET of the quads (pairsS, a subset of pairs: the shell rule,
+ * rt_scene_layout.h): one ascending pass, so the closest hit's tie rule is untouched; whether a quad's shadow half
+ * runs is warp-uniform. */
+__device__ __forceinline__ bool dual_hit_pairs_masked(const SceneRef<false> &sc, uint32_t pairs, uint32_t pairsS, f3 o,
+                                                      f3 dc, float tminC, float tmaxC, float &dist, uint32_t &id,
+                                                      f3 ds, float tminS, float tmaxS, bool &shadowed) {
+    float bestN = tmaxC, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+    bool sh = false;
+#pragma unroll 1
+    while (pairs) {
+        const uint32_t pa = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u;
+        uint32_t pb = pa;
+        if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
+#pragma unroll
+        for (uint32_t h = 0; h < 2; h++) {
+            const uint32_t q = h ? pb : pa, t0 = 2u * q;
+            const bool doS = (pairsS >> q) & 1u;                                   /* warp-uniform */
+            f3 w = mk(0.0f, 0.0f, 0.0f), cC = w, cS = w;
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                const uint32_t i = t0 + u;
+                const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+                const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+                if (u == 0) { w = mk(A.x, A.y, A.z) - o; cC = cross(dc, w); if (doS) cS = cross(ds, w); }
+                const float Nn = dot(w, n);
+                float N, a;
+                {
+                    float D = dot(dc, n);
+                    float U = dot(e2, cC), V = dot(e1n, cC);
+                    if (tri_accept(D, Nn, U, V, tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
+                }
+                if (doS) {
+                    float D = dot(ds, n);
+                    float U = dot(e2, cS), V = dot(e1n, cS);
+                    sh |= tri_accept(D, Nn, U, V, tminS, tmaxS, 1.0f, N, a);
+                }
+            }
+        }
+    }
+    shadowed = sh;
+    id = best;
+    dist = bestN / bestD;
+    return best != 0xffffffffu;
+}
+
+/* the closest-hit half of dual_hit_pairs alone (the shadow ray of a bounce is traced against its own, shorter quad
+ * list since the shell rule: rt_scene_layout.h) */
+__device__ __forceinline__ bool closest_hit_pairs(const SceneRef<false> &sc, uint32_t pairs, f3 o, f3 d, float tmin, float tmax,
+                                                  float &dist, uint32_t &id) {
+    float bestN = tmax, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+#pragma unroll 1
+    while (pairs) {
+        const uint32_t pa = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u;
+        uint32_t pb = pa;
+        if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
+#pragma unroll
+        for (uint32_t h = 0; h < 2; h++) {
+            const uint32_t t0 = 2u * (h ? pb : pa);
+            f3 w = mk(0.0f, 0.0f, 0.0f), c = w;
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                const uint32_t i = t0 + u;
+                const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+                const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+                if (u == 0) { w = mk(A.x, A.y, A.z) - o; c = cross(d, w); }
+                float N, a;
+                if (tri_accept(dot(d, n), dot(w, n), dot(e2, c), dot(e1n, c), tmin, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
+            }
+        }
+    }
+    id = best;
+    dist = bestN / bestD;
+    return best != 0xffffffffu;
+}
+
+/* is the segment from P to the light sample point inside the shrunk shell box?  (rt_scene_layout.h: then no shell quad
+ * can be accepted by the shadow ray; SB = centre xyz - | half extent xyz -; a NaN says no) */
+__device__ __forceinline__ bool shadow_inside_shell(const float *SB, f3 P, f3 sp) {
+    return (fabsf(P.x - SB[0]) < SB[4]) & (fabsf(P.y - SB[1]) < SB[5]) & (fabsf(P.z - SB[2]) < SB[6]) &
+           (fabsf(sp.x - SB[0]) < SB[4]) & (fabsf(sp.y - SB[1]) < SB[5]) & (fabsf(sp.z - SB[2]) < SB[6]);
+}
+#define RT_KEY_SHELL 0x80u     /* bit of keyarr[]: the shadow ray must be tested against the shell quads too */
+
 __device__ __forceinline__ bool any_hit_pairs(const SceneRef<false> &sc, uint32_t pairs, f3 o, f3 d, float tmin, float tmax) {
     bool hit = false;
 #pragma unroll 1
@@ -132,7 +220,8 @@ __device__ __forceinline__ bool any_hit_pairs(const SceneRef<false> &sc, uint32_
 template <int R, bool PERSIST>
 __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                       float4 *__restrict__ out, const RTLaunchParams p,
-                                                      const RTSceneLayout lay, float *sm, const RTTileSched ts) {
+                                                      const RTSceneLayout lay, float *sm, const RTTileSched ts,
+                                                      const RTHaltonTables ht) {
     constexpr uint32_t CAP = SortSmem<R>::CAP;
     {
         const float4 *src = (const float4 *)scene;
@@ -166,7 +255,8 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const uint32_t nb = (uint32_t)p.bounces;
     const uint32_t *grp = (const uint32_t *)(sm + lay.group);
-    const uint32_t K = grp[RT_GRP_K];
+    const uint32_t K = grp[RT_GRP_K], shellQuads = grp[RT_GRP_SHELL];
+    const float *shellBox = sm + lay.group + RT_GRP_SHELL_BOX;
     const uint32_t mwT = (lay.T + 31u) >> 5;
     uint32_t *tail = (uint32_t *)(sm + lay.words + (RT_BLOCK_THREADS / 32) * SortSmem<R>::WORDS_PER_WARP);
     /* the quads each key names: always-tested ones + those of the groups whose bit is set */
@@ -245,7 +335,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
 #pragma unroll
                 for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
                     const uint32_t idx = offset + (ibase + s + q);
-                    float jx = halton<0>(idx), jy = halton<1>(idx);
+                    float jx = halton<0>(idx), jy = halton_cam_y(ht, idx);
                     float sx = ((fx + jx) / resX) * 2.0f - 1.0f;
                     float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
                     rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
@@ -294,19 +384,20 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 if (active) {
                     const uint32_t slot = hitlist[e], id = idarr[slot];
                     const uint32_t i = offs[slot & 31u] + (ibase + (slot >> 5));
+                    const float4 h4 = halton_bounce4(ht, i, b);                                 /* :72-73, :93-94 */
                     const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
                     f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
                     const float *sh = sm + lay.shade + id;
                     const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
                     const f3 diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
                     const f3 P = hp + normal * 1e-3f;                                           /* raytrace.metal:67 */
-                    float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
+                    const float wx = h4.x, wy = h4.y;                                           /* :72-73 */
                     color = color * diffuse;                                                    /* :76 */
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
                     if (cont) {
                         const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
                         const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
-                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        const float ux = h4.z, uy = h4.w;                                       /* :93-94 */
                         f3 sdir = sample_cosine_hemisphere(ux, uy);
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
                     }
@@ -327,7 +418,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     if (cont) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
                     SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
                     SF(9, slot) = sp.x; SF(10, slot) = sp.z;
-                    keyarr[slot] = (uint8_t)key;
+                    keyarr[slot] = (uint8_t)(key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
                 }
                 if (sort) {
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
@@ -356,7 +447,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     const uint32_t e = c0 + lane;
                     const bool active = e < count;
                     const uint32_t slot = active ? hitlist[e] : 0u;
-                    const uint32_t key = active ? keyarr[slot] : 0xffu;
+                    const uint32_t key = active ? (keyarr[slot] & (RT_SORT_KEYS - 1u)) : 0xffu;
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
                     const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
                     uint32_t start = 0u;
@@ -379,7 +470,10 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 const uint32_t slot = active ? order[e] : 0u;
                 const uint32_t key = active ? keyarr[slot] : 0u;
                 __syncwarp();                                                  /* the chunk's entries are read: the hit list may be rewritten */
-                const uint32_t pairs = keyPairs[__reduce_or_sync(0xffffffffu, key)];
+                const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
+                const uint32_t pairs = keyPairs[keys & (RT_SORT_KEYS - 1u)];
+                /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box */
+                const uint32_t pairsS = (keys & RT_KEY_SHELL) ? pairs : (pairs & ~shellQuads);
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {
@@ -389,15 +483,32 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                     light_direction(mk(SF(9, slot), L[1], SF(10, slot)), P, ldir, ldist, inv);  /* sampling.metal:214-220 */
                     const float ltmax = ldist - 1e-3f;                                          /* raytrace.metal:81 */
                     const uint32_t surf = idarr[slot];
-                    bool shadowed, hitC = false;
+                    bool hitC = false;
                     float dist = 0.0f;
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
+#if RT_EXP_TRACE == 0
                     if (cont) {
                         rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
-                        hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);   /* :49, :79-88 */
-                    } else {
-                        shadowed = any_hit_pairs(sc, pairs, P, ldir, 0.0f, ltmax);
+                        hitC = closest_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id);   /* :49 */
                     }
+                    const bool shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);       /* :79-88 */
+#elif RT_EXP_TRACE == 1
+                    bool shadowed;
+                    if (cont) {
+                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
+                        hitC = dual_hit_pairs_masked(sc, pairs, pairsS, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
+                    } else {
+                        shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);
+                    }
+#else
+                    bool shadowed;
+                    if (cont) {
+                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
+                        hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
+                    } else {
+                        shadowed = any_hit_pairs(sc, RT_EXP_TRACE == 3 ? pairsS : pairs, P, ldir, 0.0f, ltmax);
+                    }
+#endif
                     if (!shadowed) {                                                            /* :74-75, :88 */
                         const float *sh = sm + lay.shade + surf;
                         const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);

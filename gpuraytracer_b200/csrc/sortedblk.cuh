@@ -31,7 +31,8 @@ struct SortBlkSmem {
 template <int R, bool PERSIST, bool SPATIAL = false>
 __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                          float4 *__restrict__ out, const RTLaunchParams p,
-                                                         const RTSceneLayout lay, float *sm, const RTTileSched ts) {
+                                                         const RTSceneLayout lay, float *sm, const RTTileSched ts,
+                                                         const RTHaltonTables ht) {
     static_assert(!(PERSIST && SPATIAL), "one or the other");
     constexpr uint32_t CAP = SortBlkSmem<R>::CAP, NSLOT = SortBlkSmem<R>::NSLOT;
     {
@@ -67,7 +68,8 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const uint32_t nb = (uint32_t)p.bounces;
     const uint32_t *grp = (const uint32_t *)(sm + lay.group);
-    const uint32_t K = grp[RT_GRP_K];
+    const uint32_t K = grp[RT_GRP_K], shellQuads = grp[RT_GRP_SHELL];
+    const float *shellBox = sm + lay.group + RT_GRP_SHELL_BOX;
     const uint32_t mwT = (lay.T + 31u) >> 5;
     uint32_t *tail = (uint32_t *)(sm + lay.words + SortBlkSmem<R, SPATIAL>::WORDS);
     /* the quads each key names: always-tested ones + those of the groups whose bit is set */
@@ -139,6 +141,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
         uint32_t *hits = ctr + (((k0 - kBegin) / R) & 1u);
 
         /* ---- 1. camera rays: each warp its own pixels, survivors onto the block's hit list ------------- */
+        /* halton<1> of the two samples of a pass comes from the table (rt_device_math.cuh: RTHaltonTables), asked for
+         * one pass ahead so that the load's latency is behind the previous pass's triangle tests */
+        float jyNext[2] = { 0.0f, 0.0f };
+        if (!SPATIAL) { jyNext[0] = halton_cam_y(ht, offset + ibase); jyNext[1] = halton_cam_y(ht, offset + ibase + 1u); }
 #pragma unroll 1
         for (uint32_t s = 0; s < nround; s += 2) {
             const bool two = s + 1 < nround;
@@ -159,11 +165,14 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     if (j < nround) offs[warp * CAP + j * 32u + lane] = idx[q];
                 }
             }
+            float jyq[2] = { jyNext[0], jyNext[1] };
+            if (SPATIAL) { jyq[0] = halton_cam_y(ht, idx[0]); jyq[1] = halton_cam_y(ht, idx[1]); }
+            else if (s + 2 < nround) { jyNext[0] = halton_cam_y(ht, idx[0] + 2u); jyNext[1] = halton_cam_y(ht, idx[1] + 2u); }
             if (own[0] || own[1]) {
                 f3 rd[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
-                    float jx = halton<0>(idx[q]), jy = halton<1>(idx[q]);
+                    float jx = halton<0>(idx[q]), jy = jyq[q];
                     float sx = ((fxq[q] + jx) / resX) * 2.0f - 1.0f;
                     float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
                     rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
@@ -208,28 +217,44 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
             const bool sort = count > 32u;          /* one chunk: nothing to sort, the hit list is the order */
 
             /* -- A. shade set-up, the two rays of the bounce, the key: chunk c of the hit list by warp c % 4 -- */
+            /* (the entry's slot, Halton index and the bounce's four Halton values -- one 16-byte load from the table,
+             * rt_device_math.cuh -- are fetched one chunk ahead) */
+            uint32_t slotN = 0u, iN = 0u;
+            float4 h4N = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (warp * 32u + lane < count) {
+                slotN = hitlist[warp * 32u + lane];
+                const uint32_t ow = slotN / CAP, os = slotN - ow * CAP;        /* owner warp, its slot */
+                iN = SPATIAL ? offs[slotN] : offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
+                h4N = halton_bounce4(ht, iN, b);                               /* raytrace.metal:72-73, :93-94 */
+            }
 #pragma unroll 1
             for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
                 const uint32_t e = c0 + lane;
                 const bool active = e < count;
+                const uint32_t slot = slotN;
+                const float4 h4 = h4N;
+                if (e + RT_BLOCK_THREADS < count) {
+                    slotN = hitlist[e + RT_BLOCK_THREADS];
+                    const uint32_t ow = slotN / CAP, os = slotN - ow * CAP;
+                    iN = SPATIAL ? offs[slotN] : offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
+                    h4N = halton_bounce4(ht, iN, b);
+                }
                 uint32_t key = 0xffu;
                 if (active) {
-                    const uint32_t slot = hitlist[e], id = idarr[slot];
-                    const uint32_t ow = slot / CAP, os = slot - ow * CAP;      /* owner warp, its slot */
-                    const uint32_t i = SPATIAL ? offs[slot] : offs[ow * 32u + (os & 31u)] + (ibase + (os >> 5));
+                    const uint32_t id = idarr[slot];
                     const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
                     f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
                     const float *sh = sm + lay.shade + id;
                     const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
                     const f3 diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
                     const f3 P = hp + normal * 1e-3f;                                           /* raytrace.metal:67 */
-                    float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
+                    const float wx = h4.x, wy = h4.y;                                           /* :72-73 */
                     color = color * diffuse;                                                    /* :76 */
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
                     if (cont) {
                         const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
                         const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
-                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        const float ux = h4.z, uy = h4.w;                                       /* :93-94 */
                         f3 sdir = sample_cosine_hemisphere(ux, uy);
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
                     }
@@ -250,7 +275,8 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     if (cont) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
                     SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
                     SF(9, slot) = sp.x; SF(10, slot) = sp.z;
-                    keyarr[slot] = (uint8_t)key;
+                    /* can the shadow ray skip the shell quads?  (rt_scene_layout.h; sorted.cuh: shadow_inside_shell) */
+                    keyarr[slot] = (uint8_t)(key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
                 }
                 if (sort) {
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
@@ -279,7 +305,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     const uint32_t e = c0 + lane;
                     const bool active = e < count;
                     const uint32_t slot = active ? hitlist[e] : 0u;
-                    const uint32_t key = active ? keyarr[slot] : 0xffu;
+                    const uint32_t key = active ? (keyarr[slot] & (RT_SORT_KEYS - 1u)) : 0xffu;
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
                     const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
                     uint32_t at = 0u;
@@ -304,7 +330,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 const uint32_t slot = active ? order[e] : 0u;
                 const uint32_t key = active ? keyarr[slot] : 0u;
                 __syncwarp();                                                  /* (unsorted single chunk: its entries are read before the list is rewritten) */
-                const uint32_t pairs = keyPairs[__reduce_or_sync(0xffffffffu, key)];
+                const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
+                const uint32_t pairs = keyPairs[keys & (RT_SORT_KEYS - 1u)];
+                /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box */
+                const uint32_t pairsS = (keys & RT_KEY_SHELL) ? pairs : (pairs & ~shellQuads);
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {
@@ -314,15 +343,32 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     light_direction(mk(SF(9, slot), L[1], SF(10, slot)), P, ldir, ldist, inv);  /* sampling.metal:214-220 */
                     const float ltmax = ldist - 1e-3f;                                          /* raytrace.metal:81 */
                     const uint32_t surf = idarr[slot];
-                    bool shadowed, hitC = false;
+                    bool hitC = false;
                     float dist = 0.0f;
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
+#if RT_EXP_TRACE == 0
                     if (cont) {
                         rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
-                        hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);   /* :49, :79-88 */
-                    } else {
-                        shadowed = any_hit_pairs(sc, pairs, P, ldir, 0.0f, ltmax);
+                        hitC = closest_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id);   /* :49 */
                     }
+                    const bool shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);       /* :79-88 */
+#elif RT_EXP_TRACE == 1
+                    bool shadowed;
+                    if (cont) {
+                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
+                        hitC = dual_hit_pairs_masked(sc, pairs, pairsS, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
+                    } else {
+                        shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);
+                    }
+#else
+                    bool shadowed;
+                    if (cont) {
+                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
+                        hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
+                    } else {
+                        shadowed = any_hit_pairs(sc, RT_EXP_TRACE == 3 ? pairsS : pairs, P, ldir, 0.0f, ltmax);
+                    }
+#endif
                     if (!shadowed) {                                                            /* :74-75, :88 */
                         const float *sh = sm + lay.shade + surf;
                         const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);

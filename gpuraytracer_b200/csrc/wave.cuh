@@ -97,7 +97,8 @@ template <bool COUNT, int UNROLL, int R, bool PERSIST, bool SPATIAL>
 __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                     float4 *__restrict__ out, const RTLaunchParams p,
                                                     const RTSceneLayout lay, float *sm,
-                                                    unsigned long long *__restrict__ counters, const RTTileSched ts) {
+                                                    unsigned long long *__restrict__ counters, const RTTileSched ts,
+                                                    const RTHaltonTables ht) {
     constexpr uint32_t CAP = WaveSmem<R>::CAP;
     {
         const float4 *src = (const float4 *)scene;
@@ -222,7 +223,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                 f3 rd[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {                                  /* sampling.metal:141-147 */
-                    float jx = halton<0>(idx[q]), jy = halton<1>(idx[q]);
+                    float jx = halton<0>(idx[q]), jy = halton_cam_y(ht, idx[q]);
                     float sx = ((fxq[q] + jx) / resX) * 2.0f - 1.0f;
                     float ty = -(((fy + jy) / resY) * 2.0f - 1.0f);
                     rd[q] = normalize((cam_u * (sx * halfW) + cam_v * (ty * halfH)) - cam_w);
@@ -280,6 +281,8 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     acc = mk(QF(6, e), QF(7, e), QF(8, e));
                     id = QU(9, e); i = QU(10, e); tag = QU(11, e);
                 }
+                /* the bounce's four Halton values: one load from the table (rt_device_math.cuh: RTHaltonTables) */
+                const float4 h4 = active ? halton_bounce4(ht, i, b) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 __syncwarp();                                                  /* chunk is in registers: slots may be reused */
                 if (active) {
                     f3 normal, right, fwd, diffuse;
@@ -300,14 +303,14 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     }
                     f3 P = hp + normal * 1e-3f;                                                 /* raytrace.metal:67 */
                     if (COUNT) { cnt.shaded++; cnt.shadow += numLights; }
-                    float wx = halton_slot<0>(i, b), wy = halton_slot<1>(i, b);                 /* :72-73 */
+                    const float wx = h4.x, wy = h4.y;                                           /* :72-73 */
                     color = color * diffuse;                                                    /* :76 */
                     /* the continuation ray starts at the same point as the shadow ray: it is sampled first
                      * and traced together with the first light's shadow ray (dual_hit) */
                     const bool cont = b + 1 < nb;                                               /* warp-uniform */
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
                     if (cont) {
-                        float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);             /* :93-94 */
+                        const float ux = h4.z, uy = h4.w;                                       /* :93-94 */
                         f3 sdir = sample_cosine_hemisphere(ux, uy);
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
                         if (COUNT) cnt.closest++;

@@ -9,8 +9,10 @@
  *                         on every axis or holds a light's centre is always tested; up to 4 others get a box
  *                         (bounds grown by 1/128 of the scene's largest extent) and a key bit
  *   rt_oracle_cullcheck   traces a frame with the oracle and, for EVERY ray query of it, repeats the query against
- *                         only the quads of the groups whose box the ray does not stay clear of: hit / miss,
- *                         primitive id and distance must be the full query's, bit for bit.  Also counts the keys.
+ *                         only the quads of the groups whose box the ray does not stay clear of -- and, for a shadow
+ *                         ray whose two ends (shading point, light sample point) lie inside the shrunk shell box,
+ *                         without the shell quads (sortedblk.cuh pass A / B) --: hit / miss, primitive id and
+ *                         distance must be the full query's, bit for bit.  Also counts the keys.
  *
  * The reference has no counterpart (its queries go to Metal's acceleration structure); nothing here is part of
  * the arithmetic contract -- a group only says which quads a ray may skip.
@@ -20,10 +22,12 @@
 #include <string.h>
 
 #define RT_MAX_GROUPS 4
-#define RT_GROUP_WORDS (4 + 8 * RT_MAX_GROUPS)
+#define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
+#define RT_GROUP_WORDS (RT_GRP_SHELL_BOX + 8)
 
 extern void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
                                     int hit, float distance, uint32_t primitive_id);
+extern _Thread_local float rt_oracle_light_sample[3];     /* rt_oracle.c: the sample point the shadow ray aims at */
 
 int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L,
                      uint32_t out[RT_GROUP_WORDS]) {
@@ -88,7 +92,23 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
             always |= pairs;
         }
     }
-    out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u;
+    /* the shell (rt_scene_layout.h): always-tested quads lying in a face plane of the always-tested quads' own bounds;
+     * then those bounds as centre | half extent shrunk by 1/16384 of the scene's largest extent */
+    float alo[3] = { INFINITY, INFINITY, INFINITY }, ahi[3] = { -INFINITY, -INFINITY, -INFINITY };
+    for (uint32_t p = 0; p < P; p++)
+        if ((always >> p) & 1u)
+            for (int k = 0; k < 3; k++) { alo[k] = fminf(alo[k], lo[p][k]); ahi[k] = fmaxf(ahi[k], hi[p][k]); }
+    uint32_t shell = 0;
+    for (uint32_t p = 0; p < P; p++)
+        if ((always >> p) & 1u)
+            for (int k = 0; k < 3; k++)
+                if (lo[p][k] == hi[p][k] && (lo[p][k] == alo[k] || lo[p][k] == ahi[k])) shell |= 1u << p;
+    if (shell) {
+        float *r = (float *)out + RT_GRP_SHELL_BOX;
+        const float shrink = ext * (1.0f / 16384.0f);
+        for (int k = 0; k < 3; k++) { r[k] = (alo[k] + ahi[k]) * 0.5f; r[4 + k] = (ahi[k] - alo[k]) * 0.5f - shrink; }
+    }
+    out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u; out[3] = shell;
     return (int)K;
 }
 
@@ -107,6 +127,7 @@ static struct {
     const float *vertices; uint32_t T;
     uint64_t queries, mismatches, culledTests, fullTests;
     uint64_t keysDual[16], keysSingle[16];
+    uint64_t shadowQueries, shadowInShell;
 } g_chk;
 static _Thread_local int t_pending; static _Thread_local float t_origin[3]; static _Thread_local uint32_t t_key;
 
@@ -118,6 +139,19 @@ static void cull_hook(const float o[3], const float d[3], float tmin, float tmax
         const float *r = (const float *)g_chk.words + 4 + 8 * g;
         const float w[3] = { r[0] - o[0], r[1] - o[1], r[2] - o[2] };
         if (!ray_clear_of_box(w, r + 4, d)) { key |= 1u << g; pairs |= g_chk.words[4 + 8 * g + 3]; }
+    }
+    if (any) {
+        /* the shell rule: both ends of the shadow ray inside the shrunk box of the always-tested quads' bounds */
+        const float *bx = (const float *)g_chk.words + RT_GRP_SHELL_BOX, *sp = rt_oracle_light_sample;
+        int in = 1;
+        for (int k = 0; k < 3; k++) in = in && fabsf(o[k] - bx[k]) < bx[4 + k] && fabsf(sp[k] - bx[k]) < bx[4 + k];
+        if (in) pairs &= ~g_chk.words[3];
+#pragma omp atomic
+        g_chk.shadowQueries++;
+        if (in) {
+#pragma omp atomic
+            g_chk.shadowInShell++;
+        }
     }
     int h = 0; uint32_t id = 0, tests = 0;
     float bestN = tmax, bestD = 1.0f;
@@ -159,7 +193,9 @@ static void cull_hook(const float o[3], const float d[3], float tmin, float tmax
     }
 }
 
-/* stats: queries, mismatches, triangle tests with culling, without, then keysDual[16], keysSingle[16] */
+/* stats: queries, mismatches, triangle tests with culling, without, then keysDual[16], keysSingle[16];
+ * rt_oracle_cullcheck_shell: shadow queries, and how many of them had both ends inside the shell box */
+void rt_oracle_cullcheck_shell(uint64_t out[2]) { out[0] = g_chk.shadowQueries; out[1] = g_chk.shadowInShell; }
 int rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
                         const simd_float3 *vertices, const uint32_t *offsets, float *out,
                         const RTLaunchParams *params, uint64_t stats[36], int nthreads) {

@@ -131,6 +131,10 @@ static inline void camera_ray(const CameraGPU *camera, uint32_t ix, uint32_t iy,
  * unless the caller sets light_extent (RT_VARIANT_LIGHT_EXTENT, SURVEY N3: the
  * generalisation the TODO of :175 asks for, as directSquareLightRay :180-181 does
  * it in mode B), when right and up span the light's own width x depth. */
+/* Test hook: the light sample point of the calling thread's last sample_area_light (rt_groups.c restates the sorted
+ * kernel's culling rules, one of which looks at the shadow ray's far end). */
+_Thread_local float rt_oracle_light_sample[3];
+
 static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float uy, f3 position,
                                    f3 *lightDirection, float *lightDistance, int light_extent) {
     ux = ux * 2.0f - 1.0f;
@@ -141,6 +145,7 @@ static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float 
     f3 up = f3_make(0.0f, 0.0f, light_extent ? 0.5f * light->depth : 0.25f);
     f3 samplePosition = f3_add(f3_add(f3_ld(&light->center), f3_scale(right, ux)), f3_scale(up, uy));
 
+    rt_oracle_light_sample[0] = samplePosition.x; rt_oracle_light_sample[1] = samplePosition.y; rt_oracle_light_sample[2] = samplePosition.z;
     f3 ld = f3_sub(samplePosition, position);
     float dist = f3_length(ld);
     float inverseLightDistance = 1.0f / fmaxf(dist, 1e-3f);

@@ -94,8 +94,8 @@ def flops(cnt, T, S):
 
 
 def groups(scene):
-    """The 36 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
-    out = np.zeros(36, np.uint32)
+    """The 44 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
+    out = np.zeros(44, np.uint32)
     lib.rt_oracle_groups(vp(scene["vertices"]), C.c_uint32(scene["T"]), vp(scene["lights"]), C.c_uint32(scene["L"]), vp(out))
     return out
 
@@ -111,5 +111,8 @@ def cullcheck(scene, width, height, spp, *, bounces=3, seed=1, nthreads=0):
                                  vp(off), vp(out), C.byref(p), vp(stats), nthreads)
     if rc != 0:
         raise RuntimeError(f"rt_oracle_cullcheck returned {rc}")
+    shell = np.zeros(2, np.uint64)
+    lib.rt_oracle_cullcheck_shell(vp(shell))
     return dict(queries=int(stats[0]), mismatches=int(stats[1]), culled_tests=int(stats[2]), full_tests=int(stats[3]),
+                shadow_queries=int(shell[0]), shadow_in_shell=int(shell[1]),
                 keys_dual=stats[4:20].astype(np.int64), keys_single=stats[20:36].astype(np.int64), image=out)

@@ -14,6 +14,8 @@ def test_cornell_groups_are_room_boxes_light():
     assert always == 0b100000000000011111                  # quads 0-4 (room) and 17 (light): always tested
     assert int(g[4 + 3]) == 0b000000011111100000           # tall box: quads 5-10
     assert int(g[12 + 3]) == 0b011111100000000000          # short box: quads 11-16
+    assert int(g[3]) == 0b000000000000011111               # the shell: the five walls (the light hangs 0.01 below the ceiling)
+    assert np.allclose(g.view(np.float32)[36:39], 0.0) and np.allclose(g.view(np.float32)[40:43], 2.5 - 5.05 / 16384, atol=1e-6)
     f = g.view(np.float32)
     # tall box: centre (-1, -1.15, -1.5), 1.2 x 2.8 x 1.2 turned by 75 degrees, grown by 5.05 / 128 (the boxes reach 0.05 below the floor)
     assert np.allclose(f[4:7], [-1.0, -1.15, -1.5], atol=1e-6)
@@ -31,7 +33,9 @@ def test_culling_never_changes_a_query_cornell_frame():
     # what the sorting is for: two thirds of the bounce steps need neither box
     dual = r["keys_dual"] / r["keys_dual"].sum()
     assert dual[0] > 0.6 and dual[3] < 0.03
-    assert r["culled_tests"] < 0.55 * r["full_tests"]
+    assert r["culled_tests"] < 0.42 * r["full_tests"]
+    # the shell rule: practically every shadow ray of the box starts and ends inside the room
+    assert r["shadow_in_shell"] > 0.999 * r["shadow_queries"]
 
 
 def test_culling_never_changes_a_query_other_scenes():
