@@ -106,6 +106,10 @@ EXTRA_SIGNATURES = {
     "rtHostInitSphereScene": (C.c_int, [C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(RTHostSceneBytes)]),
     "rtHostFillOffsets": (None, [P, C.c_int, C.c_int, C.c_int, C.c_uint32]),
     "rtDebugEvaluate": (C.c_int, [P, C.c_int, P, C.c_size_t, P, C.c_size_t, C.c_uint32]),
+    "rtDebugSetTuning": (C.c_int, [P, C.c_char_p, C.c_int]),
+    "rtDebugMeasureFp32Peak": (C.c_int, [P, C.POINTER(C.c_double)]),
+    "rtDebugChooseKernel": (C.c_int, [C.POINTER(RTLaunchParams), C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_char_p, C.c_size_t,
+                                      C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
 }
 for _name, (_res, _args) in {**SIGNATURES, **EXTRA_SIGNATURES}.items():
     _f = getattr(lib, _name)          # AttributeError here = the library lacks a declared symbol

@@ -48,6 +48,16 @@ class Device(_Handle):
         check(lib.rtDeviceGetInfo(self.h, C.byref(i)), "rtDeviceGetInfo")
         return i
 
+    def set_tuning(self, key, value):
+        """A/B knob of this device (csrc/rt_plan.h RTTuning; not part of rtcuda.h): tests and profiling only."""
+        check(lib.rtDebugSetTuning(self.h, key.encode(), int(value)), "rtDebugSetTuning")
+
+    def measure_fp32_peak(self):
+        """(FFMA, FFMA2) TFLOP/s of an FMA-only kernel on this device (csrc/pathtrace.cu: rt_fp32_peak), ~10 ms."""
+        t = (C.c_double * 2)()
+        check(lib.rtDebugMeasureFp32Peak(self.h, t), "rtDebugMeasureFp32Peak")
+        return t[0], t[1]
+
     def make_buffer(self, data=None, length=None):
         return Buffer(self, data, length)
 
@@ -153,6 +163,19 @@ class Command(_Handle):
         n = C.c_int()
         check(lib.rtCommandGetLaunchCount(self.h, C.byref(n)), "rtCommandGetLaunchCount")
         return n.value
+
+
+B200_SHAPE = dict(sm_count=148, max_smem_optin=232448, smem_per_sm=233472)
+
+
+def choose_kernel(params, kind=0, sm_count=148, max_smem_optin=232448, smem_per_sm=233472):
+    """The kernel a command with these parameters would run on a device of this shape (csrc/rt_plan.cpp), without a GPU.
+    Returns dict(kernel, smem_bytes, grid, chunks, chunk_spp)."""
+    name = C.create_string_buffer(64)
+    smem, grid, ch = C.c_uint32(), (C.c_uint32 * 2)(), (C.c_uint32 * 2)()
+    check(lib.rtDebugChooseKernel(C.byref(params), kind, sm_count, max_smem_optin, smem_per_sm, name, 64, C.byref(smem), grid, ch),
+          "rtDebugChooseKernel")
+    return dict(kernel=name.value.decode(), smem_bytes=smem.value, grid=(grid[0], grid[1]), chunks=ch[0], chunk_spp=ch[1])
 
 
 def default_params(width, height, **over):

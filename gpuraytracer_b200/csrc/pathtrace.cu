@@ -1129,8 +1129,8 @@ extern "C" __global__ void rt_build_halton(float4 *__restrict__ bounce, float *_
 }
 
 /* ----------------------------------------------------------------- resolve ---- */
-/* RTrace/image.swift:40-65: x2 exposure, Reinhard, gamma 1/2.2, clamp, *255 -> u8.
- * powf here is CUDA's (<= 2 ulp); the result is compared with +-1 LSB. */
+/* RTrace/image.swift:25-65: the [Float16] read-back of the render target, x2 exposure, Reinhard, gamma 1/2.2, clamp,
+ * *255 -> u8.  powf here is CUDA's (<= 2 ulp); the result is compared with +-1 LSB. */
 extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar4 *__restrict__ out,
                                             unsigned long long n, int divideByAlpha) {
     unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
@@ -1142,6 +1142,9 @@ extern "C" __global__ void rt_resolve_rgba8(const float4 *__restrict__ in, uchar
     for (int k = 0; k < 3; k++) {
         float value = c[k];
         if (divideByAlpha) value = value / v.w;
+        /* the reference tone-maps what it reads back from its rgba16Float target (image.swift:25-38): the value
+         * rounded to half, widened again */
+        value = __half2float(__float2half_rn(value));
         value *= 2.0f;
         value = value / (value + 1.0f);
         value = powf(value, 1.0f / 2.2f);
@@ -1163,6 +1166,46 @@ extern "C" __global__ void rt_resolve_rgba16f(const float4 *__restrict__ in, ush
     if (divideByAlpha) { v.x = v.x / v.w; v.y = v.y / v.w; v.z = v.z / v.w; v.w = 1.0f; }
     out[i] = make_ushort4(__half_as_ushort(__float2half_rn(v.x)), __half_as_ushort(__float2half_rn(v.y)),
                           __half_as_ushort(__float2half_rn(v.z)), __half_as_ushort(__float2half_rn(v.w)));
+}
+
+/* -------------------------------------------------- FP32 peak microbenchmark ---- */
+/* "an FFMA-saturating microbenchmark on the box": the measured FP32 peak bench.py reports beside the
+ * nominal SMs x 128 x 2 x clock.  Eight independent chains per thread; mode 0 = scalar FFMA (fma.rn.f32), mode 1 = the
+ * packed fma.rn.f32x2 of sm_100 (tools/fp32_peak.cu has the same loops plus the ALU mixes; 70.2 / 74.1 TFLOP/s in r01v). */
+extern "C" __global__ void __launch_bounds__(256) rt_fp32_peak(const float *__restrict__ in, float *__restrict__ out, int iters, int mode) {
+    float a[8];
+    const float b = in[0], c = in[1];
+    unsigned long long pk[8], pb, pc;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        a[k] = in[2 + k] + (float)threadIdx.x;
+        asm("mov.b64 %0, {%1,%2};" : "=l"(pk[k]) : "f"(a[k]), "f"(a[k] + 1.0f));
+    }
+    asm("mov.b64 %0, {%1,%2};" : "=l"(pb) : "f"(b), "f"(b));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(pc) : "f"(c), "f"(c));
+    if (mode == 0) {
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[k]) : "f"(b), "f"(c));
+        }
+    } else {
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pk[k]) : "l"(pb), "l"(pc));
+        }
+    }
+    float sum = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        float lo, hi;
+        asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(pk[k]));
+        sum += a[k] + lo + hi;
+    }
+    if (sum == 123.456f) out[0] = sum;
 }
 
 /* ------------------------------------------------------------------- debug ---- */

@@ -40,15 +40,15 @@
 #ifndef RT_EXP_TRACE
 #define RT_EXP_TRACE 1         /* A/B builds (tools/build_exp.sh): 0 separate closest / shadow loops, 1 one masked loop, 2 the r03 dual loop, no shell rule, 3 = 2 with the shell rule on the last bounce */
 #endif
-#define RT_SORT_FIELDS 11      /* X.xyz (hit point, then P)  D.xyz (continuation ray)  colour.xyz  light sample point x, z */
-#define RT_SORT_KEYS   (1 << RT_MAX_GROUPS)
+/* RT_SORT_FIELDS = 11 (X.xyz: hit point, then P; D.xyz: continuation ray; colour.xyz; light sample point x, z) and
+ * RT_SORT_KEYS come from rt_kernel_smem.h */
 
 template <int R>
 struct SortSmem {
     static constexpr uint32_t CAP = 32u * R;                      /* slots per warp = paths per round; one byte names a slot */
     static_assert(CAP <= 256u, "slot numbers are bytes");
     /* fields + res.xyz + four byte lists (hit list, sorted list; surface id and key per slot) + the lanes' offsets + key counters */
-    static constexpr uint32_t WORDS_PER_WARP = (RT_SORT_FIELDS + 3u + 1u) * CAP + 32u + RT_SORT_KEYS;
+    static constexpr uint32_t WORDS_PER_WARP = rtSortedWordsPerWarp(R);
 };
 
 /* line of the ray against a grown box, w = box centre - origin, H = half extent: the three cross-product axes

@@ -18,14 +18,16 @@
 template <int R, bool SPATIAL = false>
 struct SortBlkSmem {
     static constexpr uint32_t CAP = 32u * R;                                   /* slots per warp */
-    static constexpr uint32_t NSLOT = (RT_BLOCK_THREADS / 32) * CAP;           /* slots per block */
+    static constexpr uint32_t NSLOT = rtSortedBlkSlots(R);                     /* slots per block */
+    static_assert(RT_BLOCK_THREADS == 32 * RT_BLOCK_WARPS, "rt_kernel_smem.h sizes the arrays for this block");
     static_assert(NSLOT <= 65536u, "slot numbers are 16 bits");
     /* fields + res.xyz, two 16-bit lists (hit list, sorted list), two byte arrays (surface id, key per slot),
      * the lanes' offsets, key counters (count + running), three block counters */
     /* SPATIAL (fewer samples per launch than R: G = R / spp pixel tiles side by side per warp, as pathTrace_wide):
      * the Halton index of every slot instead of one offset per lane */
     static constexpr uint32_t OFFS = SPATIAL ? NSLOT : RT_BLOCK_THREADS;
-    static constexpr uint32_t WORDS = (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + OFFS + 2u * RT_SORT_KEYS + 4u;
+    static constexpr uint32_t WORDS = rtSortedBlkCoreWords(R, SPATIAL);        /* rt_kernel_smem.h: what the host launches with */
+    static_assert(WORDS == (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + OFFS + 2u * RT_SORT_KEYS + 4u, "layout below");
 };
 
 template <int R, bool PERSIST, bool SPATIAL = false>

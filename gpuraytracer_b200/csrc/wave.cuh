@@ -26,8 +26,7 @@
  */
 #pragma once
 
-#define RT_WAVE_FIELDS 12
-#define RT_WAVE_RES 3
+#include "rt_kernel_smem.h"     /* RT_WAVE_FIELDS, RT_WAVE_RES and the sizes the host launches with */
 
 /* Work distribution of pathTrace_tiles: a unit is one 16x8-pixel block tile x one CHUNK of chunkSpp consecutive
  * samples, one unit per block, the grid is tiles x chunks blocks.  A block takes a ticket from an atomic counter
@@ -90,7 +89,7 @@ __device__ __noinline__ void tiles_publish_chunk(unsigned int *flag, uint32_t ch
 template <int R>
 struct WaveSmem {
     static constexpr uint32_t CAP = 32u * R;                                  /* paths per warp per round */
-    static constexpr uint32_t WORDS_PER_WARP = (RT_WAVE_FIELDS + RT_WAVE_RES) * CAP;
+    static constexpr uint32_t WORDS_PER_WARP = rtWaveWordsPerWarp(R);
 };
 
 template <bool COUNT, int UNROLL, int R, bool PERSIST, bool SPATIAL>

@@ -75,22 +75,29 @@ enum {
 };
 
 enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
-/* kernel variants of pathTrace (all give bit-identical images): DEFAULT picks WAVE, or SMEM when a launch
- * has fewer than 4 samples per pixel; SMEM = one thread walks one pixel's samples; CONST = the same with the
- * primitives in the constant bank; WAVE = warp-level path compaction (csrc/wave.cuh); TILES = WAVE with one
- * block per (tile, sample chunk) unit, named by a ticket from a counter, picked by DEFAULT for launches with few
- * blocks per SM (one rank's share of a multi-GPU frame); WIDE = WAVE for launches with fewer than 6 samples per
- * pixel (progressive rendering): a warp takes 6 / spp tiles side by side so that its path queue is as full;
- * SORTED = WAVE with the paths of a round sorted by the object groups their rays can reach, so that full warps
- * test only those groups' quads (csrc/sorted.cuh; scenes of <= 64 paired triangles, no spheres, one light --
- * per-warp form); SORTED_BLOCK = the same with the sort taken over the block's four warps (csrc/sortedblk.cuh;
- * what DEFAULT picks for the Cornell scene); SORTED_TILES / SORTED_BLOCK_TILES = their ticketed forms;
- * BVH = one thread per pixel, every ray query through a bounding-volume hierarchy in global memory (csrc/bvh.cuh,
- * csrc/host_bvh.h): what DEFAULT picks above 1024 triangles, where the brute-force kernels stop.
- * Flags above the low byte: COUNT_RAYS (below), and LIGHT_EXTENT: sampleAreaLight takes its sample over the
- * light's own width x depth, right = (width/2,0,0), up = (0,0,depth/2), instead of the 0.5 x 0.5 the reference
- * hard-codes (sampling.metal:207-209, the TODO SURVEY N3 names); off = the reference's literals.  Every kernel
- * form honours it, the image changes with it (the oracle takes the same flag). */
+/* Kernel variants of pathTrace: schedules of the one reference kernel, all giving bit-identical images.
+ *   DEFAULT             the library's choice, a rule table (csrc/rt_plan.cpp; tests/test_plan_cpu.py pins it per BASELINE
+ *                       config): SORTED_BLOCK for scenes that can be cut into object groups (quads, <= 64 triangles, no
+ *                       spheres, one light: the Cornell scene), its ticketed form when a launch has fewer than 8 resident
+ *                       waves of blocks and >= 64 spp (one rank's share of a multi-GPU frame), its wide form below 6 spp
+ *                       (progressive rendering); WAVE / TILES / WIDE likewise for every other scene; BVH above 1024
+ *                       triangles; SMEM when the path queues do not fit beside the scene
+ *   SMEM                one thread walks one pixel's samples (the independent second implementation the tests compare with)
+ *   CONST               the same with the primitives in the constant bank
+ *   WAVE                warp-level path compaction (csrc/wave.cuh)
+ *   TILES               WAVE with one block per (tile, sample chunk) unit, named by a ticket from a counter
+ *   WIDE                WAVE for launches with fewer than 6 samples per pixel: a warp takes 6 / spp tiles side by side
+ *   SORTED              WAVE with the paths of a round sorted by the object groups their rays can reach, so that full warps
+ *                       test only those groups' quads (csrc/sorted.cuh; per-warp sort)
+ *   SORTED_BLOCK        the sort taken over the block's four warps (csrc/sortedblk.cuh)
+ *   SORTED_TILES, SORTED_BLOCK_TILES   their ticketed forms
+ *   BVH                 one thread per pixel, every ray query through a bounding-volume hierarchy in global memory
+ *                       (csrc/bvh.cuh), built on the device when the acceleration structure is created
+ * A form that does not apply to the launch (scene cannot be grouped, too few samples, counting requested) falls back as
+ * the table says.  Flags above the low byte: COUNT_RAYS (below); LIGHT_EXTENT: sampleAreaLight takes its sample over the
+ * light's own width x depth, right = (width/2,0,0), up = (0,0,depth/2), instead of the 0.5 x 0.5 the reference hard-codes
+ * (sampling.metal:207-209, the TODO SURVEY N3 names); off = the reference's literals.  Every kernel form honours it, the
+ * image changes with it (the oracle takes the same flag). */
 enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17, RT_VARIANT_SORTED = 18, RT_VARIANT_SORTED_TILES = 19, RT_VARIANT_SORTED_BLOCK = 20, RT_VARIANT_SORTED_BLOCK_TILES = 21, RT_VARIANT_BVH = 22,
        RT_VARIANT_COUNT_RAYS = 0x100, RT_VARIANT_LIGHT_EXTENT = 0x200 };
 
@@ -164,7 +171,10 @@ int rtQueueRelease(RTQueue *queue);
  * host pointer valid until release; if a command wrote the buffer since the
  * last call, the device copy is fetched first (after rtWaitUntilCompleted this
  * is what .contents() shows on unified memory).  After writing through the
- * pointer call rtBufferDidModifyRange (MTLBuffer.didModifyRange). */
+ * pointer call rtBufferDidModifyRange (MTLBuffer.didModifyRange): the range is copied
+ * to the device in stream order behind the last command that used the buffer, without
+ * a host-side wait; do not write it again before the next rtBufferContents call
+ * (which waits for that stream). */
 int      rtBufferCreate(RTDevice *device, const void *bytesOrNull, size_t length, RTBuffer **out);
 /* Wrap device memory owned by someone else (a torch tensor); no host mirror. */
 int      rtBufferCreateWithDevicePointer(RTDevice *device, uint64_t devicePointer, size_t length, RTBuffer **out);

@@ -385,11 +385,26 @@ int rt_oracle_intersect_ordered(const simd_float3 *vertices, const uint32_t *ids
 
 /* RTrace/image.swift:40-65.  pow() is the one place the host image writer uses
  * libm; the GPU resolve kernel is checked against this with +-1 LSB. */
+static uint16_t f32_to_f16_rne(float f);
+static float f16_to_f32(uint16_t h) {
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16, e = (h >> 10) & 0x1fu, m = h & 0x3ffu;
+    uint32_t x;
+    if (e == 0x1fu) x = sign | 0x7f800000u | (m << 13);
+    else if (e) x = sign | ((e + 112u) << 23) | (m << 13);
+    else if (!m) x = sign;
+    else { int k = 0; uint32_t mm = m; while (!(mm & 0x400u)) { mm <<= 1; k++; } x = sign | ((uint32_t)(113 - k) << 23) | ((mm & 0x3ffu) << 13); }
+    float f;
+    memcpy(&f, &x, 4);
+    return f;
+}
+
+/* image.swift:25-65: the render target is rgba16Float (renderer.swift:74-82), so what saveTextureToImage tone-maps
+ * is the shader's value rounded to half and widened again (Float(Float16)); then x2 exposure, Reinhard, gamma 2.2 */
 void rt_oracle_tonemap_rgba8(const float *rgba, uint8_t *out, uint64_t npixels) {
     const float exposure = 2.0f, gamma = 2.2f;
     for (uint64_t i = 0; i < npixels; i++) {
         for (int c = 0; c < 3; c++) {
-            float value = rgba[i * 4 + c];
+            float value = f16_to_f32(f32_to_f16_rne(rgba[i * 4 + c]));
             value *= exposure;
             value = value / (value + 1.0f);
             value = powf(value, 1.0f / gamma);

@@ -304,7 +304,7 @@ def test_camera_candidate_lists_moved_cameras(dev, scene_name):
         assert np.array_equal(img, ref), (pos, "wave", int((img != ref).sum()))
 
 
-def test_persistent_tiles_with_sample_chunks(dev, monkeypatch):
+def test_persistent_tiles_with_sample_chunks(dev):
     """pathTrace_tiles: (8x4 tile, sample chunk) units from an atomic counter; chunk c continues the running sum of
     chunk c-1 through the output buffer.  Same bits as one pass, whatever the chunking, also with row tiles,
     ragged sizes, accumulation onto an existing image, and as the library's own choice for a small share."""
@@ -313,14 +313,14 @@ def test_persistent_tiles_with_sample_chunks(dev, monkeypatch):
     ref, _ = O.pathtrace(osc, W, H, spp)
     r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
     for chunks in ("1", "2", "3", "9"):
-        monkeypatch.setenv("RT_TILES_CHUNKS", chunks)
+        dev.set_tuning("tiles_chunks", int(chunks))
         img = r.draw(spp=spp, variant=L.VARIANT_TILES)
         assert np.array_equal(img, ref), chunks
-    monkeypatch.delenv("RT_TILES_CHUNKS")
+    dev.set_tuning("tiles_chunks", 0)
     assert np.array_equal(r.draw(spp=spp, variant=L.VARIANT_TILES), ref)
     assert np.array_equal(r.draw(spp=spp), ref)                      # default: few blocks -> the library picks tiles
     # progressive: 40 + 32 samples accumulated, second launch chunked
-    monkeypatch.setenv("RT_TILES_CHUNKS", "2")
+    dev.set_tuning("tiles_chunks", 2)
     r.clear()
     r.draw_async(spp=40, firstSample=0, accumulate=1, variant=L.VARIANT_TILES)
     r.draw_async(spp=32, firstSample=40, accumulate=1, variant=L.VARIANT_TILES).wait_until_completed()
@@ -333,6 +333,7 @@ def test_persistent_tiles_with_sample_chunks(dev, monkeypatch):
     off = np.ascontiguousarray(G.fill_offsets(W, 0, H, seed=1).reshape(H, W)[mine]).reshape(-1)
     r2 = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev, row0=row0, rows=rows, offsets=off)
     assert np.array_equal(r2.draw(spp=spp, variant=L.VARIANT_TILES, tileRows=tr, tileStride=ts), ref[mine])
+    dev.set_tuning("tiles_chunks", 0)
 
 
 def test_triangle_test_exact_zero_cases(dev):
@@ -475,14 +476,14 @@ def test_sorted_kernel_moved_cameras_bounces_and_sizes(dev, variant):
 
 
 @pytest.mark.parametrize("variant", [L.VARIANT_SORTED_TILES, L.VARIANT_SORTED_BLOCK_TILES])
-def test_sorted_tiles_with_sample_chunks(dev, monkeypatch, variant):
+def test_sorted_tiles_with_sample_chunks(dev, variant):
     W, H, spp = 200, 77, 72
     ref, _ = O.pathtrace(O.cornell(W, H), W, H, spp)
     r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
     for chunks in ("1", "2", "3", "9"):
-        monkeypatch.setenv("RT_TILES_CHUNKS", chunks)
+        dev.set_tuning("tiles_chunks", int(chunks))
         assert np.array_equal(r.draw(spp=spp, variant=variant), ref), chunks
-    monkeypatch.delenv("RT_TILES_CHUNKS")
+    dev.set_tuning("tiles_chunks", 0)
     assert np.array_equal(r.draw(spp=spp), ref)                      # default: few blocks -> the ticketed sorted form
     from gpuraytracer_b200 import distributed as D
     row0, rows, tr, ts = D.tile_params(H, 1, 3, 8)

@@ -13,7 +13,7 @@ r = G.Renderer(G.init_cornell_box(W, H), W, H, device=dev)
 first = None
 # the ticketed forms cut the samples into chunks only on large launches: force three (6 + 6 + 1 samples) so that
 # the chunk hand-over across blocks (wave.cuh: tiles_wait_for_previous_chunk / tiles_publish_chunk) runs here
-os.environ["RT_TILES_CHUNKS"] = "3"
+dev.set_tuning("tiles_chunks", 3)
 for name in ("DEFAULT", "SMEM", "CONST", "WAVE", "TILES", "SORTED", "SORTED_TILES", "SORTED_BLOCK", "SORTED_BLOCK_TILES", "BVH"):
     img = r.draw(spp=13, variant=getattr(L, "VARIANT_" + name))
     first = img if first is None else first
