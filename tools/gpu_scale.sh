@@ -1,15 +1,22 @@
 #!/bin/bash
-# Multi-GPU legs: bash tools/gpu_scale.sh "<N list>" tag   (inside gpurun --gpus max(N))
-NS=${1:-2}; TAG=${2:-r01}
+# Multi-GPU legs: bash tools/gpu_scale.sh "<N list>" tag ["<configs>"]   (inside gpurun --gpus max(N))
+# Every line carries parity of the GATHERED frame against the oracle (bench.py).
+NS=${1:-2}; TAG=${2:-r01}; CFGS=${3:-"2 3"}
 O=gpurun_out; mkdir -p $O
 nvidia-smi --query-gpu=index,name --format=csv > $O/${TAG}_smi.csv
-for N in $NS; do
-  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N \
-      bench.py --gpus $N --steps 3 --warmup 3 > $O/${TAG}_bench_n${N}.json 2> $O/${TAG}_bench_n${N}.err
-  echo "N=$N exit $?"; cut -c1-260 $O/${TAG}_bench_n${N}.json
+for c in $CFGS; do
+  for N in $NS; do
+    steps=3; [ "$c" = "3" ] && steps=2
+    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N \
+        bench.py --gpus $N --steps $steps --warmup 3 --config $c > $O/${TAG}_config_${c}_n${N}.json 2> $O/${TAG}_config_${c}_n${N}.err
+    echo "config $c N=$N exit $?"
+    python - <<PY
+import json
+try:
+    d = json.load(open("$O/${TAG}_config_${c}_n${N}.json"))
+    print("  value %.1f e2e %.1f ms/step %.3f kernel_ms %.3f parity %s" % (d["value"], d["e2e"]["value"], d["ms_per_step"], d["roofline"]["kernel_ms"], d.get("parity")))
+except Exception as e:
+    print("  (no line)", e); print(open("$O/${TAG}_config_${c}_n${N}.err").read()[-1200:])
+PY
+  done
 done
-# BASELINE.json configs[2]: 4K, 4096 spp, row tiles + NCCL gather, on the largest N
-N=$(echo $NS | awk '{print $NF}')
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29520 \
-    bench.py --gpus $N --steps 2 --warmup 3 --width 3840 --height 2160 --spp 4096 > $O/${TAG}_bench4k_n${N}.json 2> $O/${TAG}_bench4k_n${N}.err
-echo "4K N=$N exit $?"; cut -c1-260 $O/${TAG}_bench4k_n${N}.json
