@@ -94,6 +94,7 @@ SIGNATURES = {
     "rtCommandRelease": (C.c_int, [P]),
     "rtResolveToRGBA8": (C.c_int, [P, P, C.c_size_t, P, C.c_size_t, C.c_uint64, C.c_int]),
     "rtResolveToRGBA16F": (C.c_int, [P, P, C.c_size_t, P, C.c_size_t, C.c_uint64, C.c_int]),
+    "rtPathTraceNoAlloc": (C.c_int, [P, P, P, P, P, P, P, C.POINTER(RTLaunchParams), P]),
     "rtGroupCreate": (C.c_int, [C.POINTER(C.c_int), C.c_int, PP]),
     "rtGroupDeviceCount": (C.c_int, [P]),
     "rtGroupRender": (C.c_int, [P, C.c_char_p, P, P, C.c_size_t, P, C.c_size_t, P, C.c_size_t, P, C.c_size_t,

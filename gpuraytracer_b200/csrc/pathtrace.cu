@@ -993,10 +993,12 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
         extern __shared__ __align__(16) float sm[];                                                              \
         pathtrace_body<CONST_BANK, COUNT, UNROLL>(scene, offsets, out, p, lay, sm, counters);                    \
     }
+#ifndef RT_NOALLOC_BUILD   /* noalloc.cu includes this file for rt_prep_scene, the intersector and the wave body only: the default build is unchanged */
 RT_PATHTRACE_ENTRY(pathTrace_smem, false, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const, true, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
+#endif
 #include "wave.cuh"
 #define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB, SPATIAL)                                                            \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
@@ -1020,6 +1022,7 @@ RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
  * 5 392 for R = 8 with three blocks, 5 482 for R = 5, 4 889 for R = 12 with two (profiles/r02c_variants_R.txt).
  * Earlier in the kernel's life occupancy did not matter (r01c, r01h); it does since the primitive loops shrank
  * and the latency-bound code between them became a larger share. */
+#ifndef RT_NOALLOC_BUILD   /* noalloc.cu includes this file for rt_prep_scene, the intersector and the wave body only: the default build is unchanged */
 RT_WAVE_ENTRY(pathTrace_wave, false, 4, 6, 4, false)
 RT_WAVE_ENTRY(pathTrace_wave_count, true, 4, 6, 4, false)
 /* R = 4: two thirds of the queue memory; the library picks it when a large scene leaves room for fewer than
@@ -1273,3 +1276,4 @@ extern "C" __global__ void rt_debug_eval(int what, const void *__restrict__ in, 
         ((float *)out)[3 * k + 2] = hit ? a : 0.0f;
     }
 }
+#endif /* RT_NOALLOC_BUILD */

@@ -243,6 +243,28 @@ int rtResolveToRGBA8(RTQueue *queue, RTBuffer *in, size_t inOffset, RTBuffer *ou
 int rtResolveToRGBA16F(RTQueue *queue, RTBuffer *in, size_t inOffset, RTBuffer *out, size_t outOffset,
                        uint64_t pixelCount, int divideByAlpha);
 
+/* ---- pathTrace without any allocation ----------------------------------------
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Renders as a pathTrace command does (same parameters, same image bit for bit) but calls no cuMemAlloc / cudaMalloc /
+ * cudaFree nor any allocating library routine: the kernel's scratch -- the prepared scene, rt_scene_layout.h -- is a
+ * static __device__ array of 57 664 bytes inside the library (every GPU that loads it holds it until exit), and the
+ * Halton values are computed instead of read from the library's tables.
+ *   - all pointers are DEVICE pointers (rtBufferDevicePointer of a library buffer, a torch tensor's data_ptr(), ...):
+ *     camera CameraGPU[1], materials MaterialGPU[T], lights SquareLightGPU[L], vertices simd_float3[3T], spheres
+ *     SphereGPU[S] or NULL, offsets uint32[width * rows], out float4[width * rows] (this launch's rows);
+ *   - limits: numTriangles <= 256, numSpheres <= 256, numLights <= 16, else RT_ERR_OUT_OF_RANGE and nothing is
+ *     launched; params->variant may carry RT_VARIANT_LIGHT_EXTENT only (there is one kernel form);
+ *   - the device to render on must be CURRENT on the calling thread (cudaSetDevice / an rtDeviceCreate'd device's
+ *     primary context); cuStream is a CUstream / cudaStream_t of that device or NULL; the call is asynchronous;
+ *   - every call on a device shares the one scratch array, which keeps the last call's contents (each call clears
+ *     the part it uses first): calls that OVERLAP on the GPU -- two streams, or a captured graph replayed beside a
+ *     live call -- race on it.  Serialise them (one stream, or events).
+ * Returns RT_OK, an RT_ERR_* code, or > 0: a cudaError_t of the CUDA runtime. */
+int rtPathTraceNoAlloc(const void *camera, const void *materials, const void *lights, const void *vertices,
+                       const void *spheresOrNull, const uint32_t *offsets, float *out,
+                       const RTLaunchParams *params, void *cuStream);
+
 /* ---- new: one process, several GPUs, row tiles ------------------------------ */
 int rtGroupCreate(const int *ordinals, int count, RTGroup **out);
 int rtGroupDeviceCount(RTGroup *group);
