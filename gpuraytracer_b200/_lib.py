@@ -23,12 +23,14 @@ RT_ERR = {-1: "INVALID_ARGUMENT", -2: "UNKNOWN_KERNEL", -3: "NO_DRIVER", -4: "MI
 
 INDEX_CAMERA, INDEX_MATERIALS, INDEX_LIGHTS, INDEX_VERTICES, INDEX_PIXELS = 0, 1, 2, 3, 4
 INDEX_ACCEL, INDEX_DEBUG, INDEX_SPHERES, INDEX_OUTPUT, INDEX_OFFSETS = 5, 6, 7, 16, 17
+INDEX_LIGHT_NORMALS = 8        # optional float4[L] side table: the lights' normals
 FORMAT_RGBA32_FLOAT, FORMAT_R32_UINT = 1, 2
 VARIANT_DEFAULT, VARIANT_SMEM, VARIANT_CONST, VARIANT_WAVE, VARIANT_TILES, VARIANT_WIDE = 0, 1, 2, 3, 16, 17
 VARIANT_SORTED, VARIANT_SORTED_TILES, VARIANT_SORTED_BLOCK, VARIANT_SORTED_BLOCK_TILES = 18, 19, 20, 21
 VARIANT_BVH = 22
 VARIANT_COUNT_RAYS = 0x100
 VARIANT_LIGHT_EXTENT = 0x200   # flag: sampleAreaLight over the light's own width x depth
+VARIANT_MIS = 0x400            # flag: light sample + cosine-sampled continuation combined by the balance heuristic
 
 
 class RTLaunchParams(C.Structure):

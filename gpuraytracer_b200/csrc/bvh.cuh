@@ -157,6 +157,7 @@ struct RTBvhArgs { const float4 *nodes; const float4 *tris; uint32_t numNodes, p
  * shared memory instead of local memory (+-2 %).  What pays is residency: more warps hide more of the node-fetch
  * latency -- six blocks per SM (80 registers) against four +15 to +17 % at 36 to 36 864 triangles, eight (64
  * registers, 64 bytes of spills) another +3 % (profiles/r03g_bvh_forms.txt). */
+template <bool MIS = false>
 __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                    float4 *__restrict__ out, const RTLaunchParams &p, const RTSceneLayout &lay,
                                                    const RTBvhArgs &ba, float *sm, const RTHaltonTables &ht) {
@@ -203,8 +204,8 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
 #pragma unroll 1
         for (uint32_t b = 0; hit; b++) {                                /* raytrace.metal:47-101 */
             const float *sh = shade + id;
-            if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                      /* :57-60 */
-                acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
+            if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                      /* :57-60; MIS: only a camera ray takes it (mis.cuh) */
+                if (!MIS || b == 0) acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
                 break;
             }
             const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
@@ -218,9 +219,10 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
                 f3 ldir; float ldist;
                 f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));  /* :75 */
+                if (MIS) lightColor = lightColor * misA_light_weight(L, P, normal, ldir);
                 if (!bvh_any(bv, st, P, ldir, 0.0f, ldist - 1e-3f, budget)) acc = acc + lightColor * color;   /* :79-88 */
             }
-            if (b + 1 >= nb) break;
+            if (!MIS && b + 1 >= nb) break;
             const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
             const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
             const float ux = h4.z, uy = h4.w;                           /* :93-94 */
@@ -228,6 +230,11 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
             rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;     /* sampling.metal:65 */
             ro = P;                                                     /* :99-100 */
             hit = bvh_closest(bv, st, ro, rd, 0.001f, 1000.0f, budget, dist, id);
+            if (MIS) {
+                for (uint32_t l = 0; l < numLights; l++)
+                    acc = acc + misA_cosine_term(lights + RT_LIGHT_WORDS * l, P, normal, rd, hit, dist, color);
+                if (b + 1 >= nb) break;
+            }
         }
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
@@ -237,16 +244,17 @@ __device__ __forceinline__ void pathtrace_bvh_body(const float *__restrict__ sce
     out[pix] = o;
 }
 
-#define RT_BVH_ENTRY(name, MINB)                                                                                 \
+#define RT_BVH_ENTRY(name, MINB, MIS)                                                                                 \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
     name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
          const RTLaunchParams p, const RTSceneLayout lay, const RTBvhArgs ba, const RTHaltonTables ht) {         \
         extern __shared__ __align__(16) float sm[];          /* header, then the lights */                       \
-        pathtrace_bvh_body(scene, offsets, out, p, lay, ba, sm, ht);                                             \
+        pathtrace_bvh_body<MIS>(scene, offsets, out, p, lay, ba, sm, ht);                                        \
     }
-RT_BVH_ENTRY(pathTrace_bvh, 8)
+RT_BVH_ENTRY(pathTrace_bvh, 8, false)
+RT_BVH_ENTRY(pathTrace_bvh_mis, 8, true)
 #ifdef RT_TUNING_VARIANTS   /* RT_BVH_FORM=<suffix> (rtcuda.cpp), tools/time_bvh.py: blocks per SM */
-RT_BVH_ENTRY(pathTrace_bvh_l4, 4)
-RT_BVH_ENTRY(pathTrace_bvh_l6, 6)
-RT_BVH_ENTRY(pathTrace_bvh_l10, 10)
+RT_BVH_ENTRY(pathTrace_bvh_l4, 4, false)
+RT_BVH_ENTRY(pathTrace_bvh_l6, 6, false)
+RT_BVH_ENTRY(pathTrace_bvh_l10, 10, false)
 #endif

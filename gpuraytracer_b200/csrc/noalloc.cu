@@ -117,7 +117,7 @@ extern "C" int rtPathTraceNoAlloc(const void *camera, const void *materials, con
     }
     if (p.bounces < 1 || p.bounces > 4)
         return naFail(RT_ERR_UNSUPPORTED, "bounces = %d; Halton dimension 2+5b+3 must stay inside primes[24] (1..4)", p.bounces);
-    if (p.variant & ~(uint32_t)RT_VARIANT_LIGHT_EXTENT)
+    if (p.variant & ~(uint32_t)RT_VARIANT_LIGHT_EXTENT)      /* (RT_VARIANT_MIS included: this entry point has the reference's estimator only) */
         return naFail(RT_ERR_UNSUPPORTED, "rtPathTraceNoAlloc has one kernel form: variant may carry RT_VARIANT_LIGHT_EXTENT only");
     if (p.numTriangles == 0 || p.numTriangles > RT_NOALLOC_MAX_TRIANGLES || p.numSpheres > RT_NOALLOC_MAX_SPHERES || p.numLights > RT_NOALLOC_MAX_LIGHTS)
         return naFail(RT_ERR_OUT_OF_RANGE, "rtPathTraceNoAlloc: scene of %u triangles, %u spheres, %u lights exceeds the static scratch "
@@ -147,7 +147,8 @@ extern "C" int rtPathTraceNoAlloc(const void *camera, const void *materials, con
     /* the array keeps the last call's contents: clear what this call uses, then prep rewrites every word the tracer reads */
     if ((e = cudaMemsetAsync(d->scene, 0, sceneBytes, stream)) != cudaSuccess) return naCuda(e, "cudaMemsetAsync");
     rt_noalloc_prep_scene<<<1, 256, 0, stream>>>((const unsigned char *)camera, (const unsigned char *)materials, (const unsigned char *)lights,
-                                                 (const unsigned char *)vertices, (const unsigned char *)spheresOrNull, d->scene, lay);
+                                                 (const unsigned char *)vertices, (const unsigned char *)spheresOrNull, d->scene, lay,
+                                                 (const float4 *)nullptr);
     if ((e = cudaGetLastError()) != cudaSuccess) return naCuda(e, "launch of rt_prep_scene");
     const dim3 grid((unsigned)((p.width + 15) / 16), (unsigned)((p.rows + 7) / 8));
     if (r6) pathTrace_noalloc6<<<grid, RT_BLOCK_THREADS, smem, stream>>>(d->scene, offsets, (float4 *)out, p, lay);

@@ -177,7 +177,8 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
                                          const unsigned char *__restrict__ lights,
                                          const unsigned char *__restrict__ vertices,
                                          const unsigned char *__restrict__ spheres,
-                                         float *__restrict__ scene, RTSceneLayout lay) {
+                                         float *__restrict__ scene, RTSceneLayout lay,
+                                         const float4 *__restrict__ lightNormals) {
     const int tid = threadIdx.x, nth = blockDim.x;
     const float *cam = (const float *)camera;
     const f3 position = mk(cam[0], cam[1], cam[2]);
@@ -289,8 +290,21 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         const bool extent = (lay.flags & RT_LAYOUT_LIGHT_EXTENT) != 0u;
         d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = extent ? 0.5f * s[12] : 0.25f;   /* right.x, sampling.metal:208 */
         d[4] = s[4]; d[5] = s[5]; d[6] = s[6]; d[7] = extent ? 0.5f * s[13] : 0.25f;   /* up.z,    sampling.metal:209 */
-        d[8] = s[8]; d[9] = s[9]; d[10] = s[10]; d[11] = 0.0f;            /* emittedRadiance@32 */
+        d[8] = s[8]; d[9] = s[9]; d[10] = s[10];                          /* emittedRadiance@32 */
         d[12] = s[12]; d[13] = s[13]; d[14] = 0.0f; d[15] = 0.0f;         /* width@48 depth@52  */
+        /* the light's normal and the basis of its sample rectangle: the reference's literals, or -- with a
+         * normal table bound -- the table's normal and buildOrthonormalBasis of it (sampling.metal:158-171) */
+        const bool general = (lay.flags & RT_LAYOUT_LIGHT_NORMALS) != 0u && lightNormals != nullptr;
+        f3 nL = mk(0.0f, -1.0f, 0.0f), tg = mk(1.0f, 0.0f, 0.0f), bt = mk(0.0f, 0.0f, 1.0f);
+        if (general) {
+            const float4 t = lightNormals[l];
+            nL = normalize(mk(t.x, t.y, t.z));
+            orthonormal_basis(nL, tg, bt);
+        }
+        ((uint32_t *)d)[RT_LIGHT_GENERAL] = general ? 1u : 0u;
+        d[RT_LIGHT_NORMAL] = nL.x; d[RT_LIGHT_NORMAL + 1] = nL.y; d[RT_LIGHT_NORMAL + 2] = nL.z; d[RT_LIGHT_NORMAL + 3] = 0.0f;
+        d[RT_LIGHT_TANGENT] = tg.x; d[RT_LIGHT_TANGENT + 1] = tg.y; d[RT_LIGHT_TANGENT + 2] = tg.z; d[RT_LIGHT_TANGENT + 3] = 0.0f;
+        d[RT_LIGHT_BITANGENT] = bt.x; d[RT_LIGHT_BITANGENT + 1] = bt.y; d[RT_LIGHT_BITANGENT + 2] = bt.z; d[RT_LIGHT_BITANGENT + 3] = 0.0f;
     }
 }
 
@@ -828,9 +842,22 @@ __device__ __forceinline__ f3 light_colour(f3 lcolor, float inv, f3 ldir) {
 __device__ __forceinline__ f3 sample_area_light(const float *L, float ux, float uy, f3 P, f3 &ldir, float &ldist) {
     const f3 lcolor = mk(L[4], L[5], L[6]);
     float inv;
+    if (((const uint32_t *)L)[RT_LIGHT_GENERAL] != 0u) {
+        /* a light with a normal of its own (prepared by rt_prep_scene): sampling.metal:198-236 written out over
+         * right = tangent * hx, up = bitangent * hz and that normal -- nothing folds to zero here */
+        ux = ux * 2.0f - 1.0f;
+        uy = uy * 2.0f - 1.0f;
+        const f3 right = mk(L[RT_LIGHT_TANGENT], L[RT_LIGHT_TANGENT + 1], L[RT_LIGHT_TANGENT + 2]) * L[3];
+        const f3 up = mk(L[RT_LIGHT_BITANGENT], L[RT_LIGHT_BITANGENT + 1], L[RT_LIGHT_BITANGENT + 2]) * L[7];
+        const f3 sp = (mk(L[0], L[1], L[2]) + right * ux) + up * uy;
+        light_direction(sp, P, ldir, ldist, inv);
+        f3 c = lcolor * (inv * inv);
+        return c * saturate(dot(-ldir, mk(L[RT_LIGHT_NORMAL], L[RT_LIGHT_NORMAL + 1], L[RT_LIGHT_NORMAL + 2])));
+    }
     light_direction(light_sample_point(mk(L[0], L[1], L[2]), L[3], L[7], ux, uy), P, ldir, ldist, inv);
     return light_colour(lcolor, inv, ldir);
 }
+#include "mis.cuh"
 
 /* sampling.metal:39-49 */
 __device__ __forceinline__ f3 sample_cosine_hemisphere(float ux, float uy) {
@@ -859,7 +886,7 @@ struct Counters { uint32_t closest, shadow, shaded; };
  * uniform datapath (halton_slot).  Bounce 0 uses the camera-ray form of the
  * triangle test.
  */
-template <bool CONST_BANK, bool COUNT, int UNROLL>
+template <bool CONST_BANK, bool COUNT, int UNROLL, bool MIS = false>
 __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                float4 *__restrict__ out, const RTLaunchParams p,
                                                const RTSceneLayout lay, float *sm,
@@ -924,7 +951,8 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
             if (id < lay.T) {
                 const float *sh = sm + lay.shade + id;
                 if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                          /* :57-60 */
-                    acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
+                    /* (MIS: only a camera ray takes the emissive, mis.cuh) */
+                    if (!MIS || b == 0) acc = mk(sh[(RT_SH_ER + 0) * lay.Tp], sh[(RT_SH_ER + 1) * lay.Tp], sh[(RT_SH_ER + 2) * lay.Tp]);
                     break;
                 }
                 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
@@ -935,7 +963,7 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
                 uint32_t j = id - lay.T;
                 const float *sh = sm + lay.sshade + j;
                 if (sh[RT_SSH_FLAG * lay.Sp] != 0.0f) {
-                    acc = mk(sh[(RT_SSH_ER + 0) * lay.Sp], sh[(RT_SSH_ER + 1) * lay.Sp], sh[(RT_SSH_ER + 2) * lay.Sp]);
+                    if (!MIS || b == 0) acc = mk(sh[(RT_SSH_ER + 0) * lay.Sp], sh[(RT_SSH_ER + 1) * lay.Sp], sh[(RT_SSH_ER + 2) * lay.Sp]);
                     break;
                 }
                 const float *S = sm + lay.sphere + RT_SPHERE_WORDS * j;
@@ -955,17 +983,23 @@ __device__ __forceinline__ void pathtrace_body(const float *__restrict__ scene, 
                 f3 ldir; float ldist;
                 f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                 lightColor = lightColor * saturate(dot(normal, ldir));                          /* :75 */
+                if (MIS) lightColor = lightColor * misA_light_weight(L, P, normal, ldir);
                 /* shadow ray: default-constructed => min_distance 0; max = dist - 1e-3   :79-85 */
                 if (!any_hit<CONST_BANK, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f))
                     acc = acc + lightColor * color;                                             /* :88 */
             }
-            if (b + 1 >= nb) break;
+            if (!MIS && b + 1 >= nb) break;
             float ux = halton_slot<2>(i, b), uy = halton_slot<3>(i, b);                         /* :93-94 */
             f3 sdir = sample_cosine_hemisphere(ux, uy);
             rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                             /* sampling.metal:65 */
             ro = P;                                                                             /* :99-100 */
             if (COUNT) cnt.closest++;
             hit = closest_hit<CONST_BANK, false, UNROLL>(sc, ro, rd, 0.001f, 1000.0f, dist, id);        /* :49 */
+            if (MIS) {      /* the cosine strategy's term of every light for this continuation ray (traced after the last bounce too) */
+                for (uint32_t l = 0; l < numLights; l++)
+                    acc = acc + misA_cosine_term(sm + lay.light + RT_LIGHT_WORDS * l, P, normal, rd, hit, dist, color);
+                if (b + 1 >= nb) break;
+            }
         }
         lum = lum + acc;                                                /* raytrace.metal:103 */
     }
@@ -998,6 +1032,15 @@ RT_PATHTRACE_ENTRY(pathTrace_smem, false, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const, true, false, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_smem_count, false, true, 4, 4)
 RT_PATHTRACE_ENTRY(pathTrace_const_count, true, true, 4, 4)
+#endif
+#ifndef RT_NOALLOC_BUILD
+/* RT_VARIANT_MIS (mis.cuh): the per-pixel kernel with the two-strategy light term */
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_smem_mis(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+                   const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {
+    extern __shared__ __align__(16) float sm[];
+    pathtrace_body<false, false, 4, true>(scene, offsets, out, p, lay, sm, counters);
+}
 #endif
 #include "wave.cuh"
 #define RT_WAVE_ENTRY(name, COUNT, UNROLL, R, MINB, SPATIAL)                                                            \
@@ -1034,6 +1077,17 @@ RT_WAVE_PERSIST_ENTRY(pathTrace_tiles, false, 4, 6, 4)
 RT_WAVE_PERSIST_ENTRY(pathTrace_tiles4, false, 4, 4, 4)
 RT_WAVE_ENTRY(pathTrace_wave4, false, 4, 4, 4, false)
 RT_WAVE_ENTRY(pathTrace_wave4_count, true, 4, 4, 4, false)
+/* RT_VARIANT_MIS (mis.cuh): the compacting kernel with the two-strategy light term, R = 6 and R = 4 */
+#define RT_WAVE_MIS_ENTRY(name, R)                                                                               \
+    extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)                                            \
+    name(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,        \
+         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
+         const RTHaltonTables ht) {                                                                              \
+        extern __shared__ __align__(16) float sm[];                                                              \
+        pathtrace_wave_body<false, 4, R, false, false, true>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
+    }
+RT_WAVE_MIS_ENTRY(pathTrace_wave_mis, 6)
+RT_WAVE_MIS_ENTRY(pathTrace_wave4_mis, 4)
 #ifdef RT_TUNING_VARIANTS   /* queue depth x occupancy sweep (variants 5, 6, 10, 12 of tools/time_variants.py): tools/build_exp.sh */
 RT_WAVE_ENTRY(pathTrace_exp10, false, 4, 2, 4, false)
 RT_WAVE_ENTRY(pathTrace_exp8, false, 4, 8, 3, false)
@@ -1090,6 +1144,17 @@ RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
             pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
     }
 RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)
+/* RT_VARIANT_MIS (mis.cuh) on the sorted path; an ungrouped scene falls to the compacting kernel's MIS form */
+extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
+pathTrace_sortedblk6_mis(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,
+                         const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,
+                         const RTHaltonTables ht) {
+    extern __shared__ __align__(16) float sm[];
+    if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])
+        pathtrace_sortedblk_body<6, false, false, true>(scene, offsets, out, p, lay, sm, RTTileSched{}, ht);
+    else
+        pathtrace_wave_body<false, 4, 4, false, false, true>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht);
+}
 /* fewer samples per launch than a round has slots (progressive rendering): G = 6 / spp tiles side by side per warp */
 extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, 4)
 pathTrace_sortedblk_wide6(const float *__restrict__ scene, const uint32_t *__restrict__ offsets, float4 *__restrict__ out,

@@ -114,7 +114,7 @@ static const Rule RULES[] = {
 };
 
 int rtPlanKernel(const RTLaunchParams *pp, int kind, const RTTuning *tune, const RTDeviceShape *dev, size_t constBankBytes,
-                 RTKernelPlan *out, char *err, size_t errCap) {
+                 uint32_t layoutFlags, RTKernelPlan *out, char *err, size_t errCap) {
     const RTLaunchParams &p = *pp;
     memset(out, 0, sizeof *out);
     const uint32_t request = p.variant & 0xffu;
@@ -129,7 +129,10 @@ int rtPlanKernel(const RTLaunchParams *pp, int kind, const RTTuning *tune, const
 
     RTSceneLayout lay = rtSceneLayout(T, S, L);
     if (p.variant & RT_VARIANT_LIGHT_EXTENT) lay.flags |= RT_LAYOUT_LIGHT_EXTENT;
+    lay.flags |= layoutFlags & RT_LAYOUT_LIGHT_NORMALS;
     out->lay = lay;
+    const bool mis = kind == 0 && (p.variant & RT_VARIANT_MIS) != 0;
+    if (mis && count) return planFail(err, errCap, RT_ERR_UNSUPPORTED, "RT_VARIANT_MIS has no counting twin (COUNT_RAYS)");
     const size_t sceneBytes = (size_t)lay.words * 4, room = dev->maxSmemOptin;
     out->sceneBytes = sceneBytes;
     if (!useBvh && sceneBytes + 1024 > room)
@@ -145,7 +148,9 @@ int rtPlanKernel(const RTLaunchParams *pp, int kind, const RTTuning *tune, const
     const size_t sortedBytes = (size_t)rtSortedWords((uint32_t)sortedR, T) * 4, sorted6 = (size_t)rtSortedWords(6, T) * 4;
     const size_t blkBytes = (size_t)rtSortedBlkWords(6, false, T) * 4, blkWideBytes = (size_t)rtSortedBlkWords(6, true, T) * 4;
 
-    const bool groupable = kind == 0 && T >= 2 && T <= 64 && T % 2 == 0 && S == 0 && L == 1 && !tune->noSorted;
+    /* (a light with a normal of its own is not for the sorted kernels: they keep x and z of the light sample point only) */
+    const bool groupable = kind == 0 && T >= 2 && T <= 64 && T % 2 == 0 && S == 0 && L == 1 && !tune->noSorted &&
+                           !(lay.flags & RT_LAYOUT_LIGHT_NORMALS);
     const bool sortedOk = groupable && p.spp >= (uint32_t)sortedR && fits(sortedBytes);
     const unsigned gx = (unsigned)((p.width + 15) / 16), gy = (unsigned)((p.rows + 7) / 8);
     const unsigned long long blocks = (unsigned long long)gx * gy;
@@ -184,6 +189,20 @@ int rtPlanKernel(const RTLaunchParams *pp, int kind, const RTTuning *tune, const
         }
     }
     if (form < 0) return planFail(err, errCap, RT_ERR_INVALID_ARGUMENT, "unknown kernel variant %u", p.variant);
+    if (mis) {
+        /* RT_VARIANT_MIS (mis.cuh) exists as the per-pixel, the compacting, the block-sorted and the BVH kernel; every other
+         * form falls to the nearest of those (the image is the same whichever runs) */
+        switch (form) {
+        case RT_FORM_SMEM: case RT_FORM_CONST: form = RT_FORM_SMEM; break;
+        case RT_FORM_SORTEDBLK: case RT_FORM_SORTEDBLK_TILES: break;
+        case RT_FORM_SORTEDBLK_WIDE: case RT_FORM_BVH: break;
+        case RT_FORM_EXP: return planFail(err, errCap, RT_ERR_UNSUPPORTED, "tuning variants have no MIS twin");
+        default: form = (facts & WAVE_FITS) ? RT_FORM_WAVE : RT_FORM_SMEM; break;
+        }
+        if (form == RT_FORM_SORTEDBLK_TILES) form = RT_FORM_SORTEDBLK;
+        if (form == RT_FORM_SORTEDBLK_WIDE) form = RT_FORM_WAVE;            /* spp < 6: the compacting kernel takes any sample count */
+        out->mis = 1;
+    }
 
     out->form = form; out->count = count ? 1 : 0; out->gridX = gx; out->gridY = gy;
     const char *cnt = count ? "_count" : "";
@@ -244,6 +263,10 @@ int rtPlanKernel(const RTLaunchParams *pp, int kind, const RTTuning *tune, const
             return planFail(err, errCap, RT_ERR_UNSUPPORTED, "misSamples = %u: Halton tables do not fit shared memory", p.misSamples);
         snprintf(out->kernel, sizeof out->kernel, "drawTriangle_mis");
         break;
+    }
+    if (out->mis) {
+        const size_t n = strlen(out->kernel);
+        snprintf(out->kernel + n, sizeof out->kernel - n, "_mis");
     }
     if (form == RT_FORM_WIDE || form == RT_FORM_SORTEDBLK_WIDE) {       /* a block covers 16 G x 8 pixels, G = R / spp (wave.cuh) */
         const unsigned G = (unsigned)out->R / (p.spp ? p.spp : 1u);

@@ -56,12 +56,14 @@ struct RTKernelPlan {
     unsigned gridX, gridY;     /* blocks of 128 threads; the ticketed forms launch gridX * gridY * chunks */
     int ticketed;              /* RT_FORM_*TILES                                                     */
     int copyConst;             /* RT_FORM_CONST: the intersection part goes to the constant bank first */
+    int mis;                   /* RT_VARIANT_MIS: the form's two-strategy twin (kernel name ends in _mis)   */
 };
 
 /* p: the command's parameters with the counts resolved (numTriangles, numLights != 0).  kind: 0 pathTrace, 1 drawTriangle.
  * Returns RT_OK or an RT_ERR_* with the text in err. */
+/* layoutFlags: RT_LAYOUT_* the caller knows beyond p->variant (RT_LAYOUT_LIGHT_NORMALS when a normal table is bound). */
 int rtPlanKernel(const RTLaunchParams *p, int kind, const RTTuning *tune, const RTDeviceShape *dev, size_t constBankBytes,
-                 RTKernelPlan *out, char *err, size_t errCap);
+                 uint32_t layoutFlags, RTKernelPlan *out, char *err, size_t errCap);
 
 /* how the ticketed forms cut the samples into chunks: blockTiles x chunks units for `resident` block slots */
 void rtPlanChunks(const RTLaunchParams *p, const RTKernelPlan *plan, const RTTuning *tune, unsigned long long resident,

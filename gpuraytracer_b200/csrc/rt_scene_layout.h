@@ -20,7 +20,7 @@
  *            up to 4): looked up with the per-lane primitive id after a hit,
  *            so SoA keeps different ids on different banks
  *   sshade : RT_SSHADE_ROWS rows of Sp words
- *   light  : 16 words per light     center.xyz 0 | color.xyz 0 | emittedRadiance.xyz 0 | width depth 0 0
+ *   light  : RT_LIGHT_WORDS per light (see the define below)
  *   group  : RT_GROUP_WORDS words: object groups for the sorted kernel (sorted.cuh), built by rt_prep_scene
  *            when every triangle 2k+1 shares v0 with 2k (pairs), T <= 64 and S == 0:
  *            [0] K = number of cullable groups (0..4)   [1] pair mask that is always tested
@@ -75,9 +75,18 @@
 #define RT_SSH_FLAG       6
 #define RT_SSHADE_ROWS    7
 
-#define RT_LIGHT_WORDS   16   /* center.xyz hx | color.xyz hz | emittedRadiance.xyz 0 | width depth 0 0;  (hx,hz) = half extent
-                                 sampleAreaLight uses: 0.25, 0.25 (sampling.metal:207-209) or width/2, depth/2 (RT_LAYOUT_LIGHT_EXTENT) */
+#define RT_LIGHT_WORDS   28   /* center.xyz hx | color.xyz hz | emittedRadiance.xyz general | width depth 0 0 | normal.xyz 0 |
+                                 tangent.xyz 0 | bitangent.xyz 0.   (hx,hz) = half extent of the rectangle sampleAreaLight samples:
+                                 0.25, 0.25 (sampling.metal:207-209) or width/2, depth/2 (RT_LAYOUT_LIGHT_EXTENT).
+                                 normal / tangent / bitangent: (0,-1,0), (1,0,0), (0,0,1) -- the reference's literals -- and
+                                 general = 0, unless a normal table is bound (RT_LAYOUT_LIGHT_NORMALS): then the table's
+                                 normal, normalised, with buildOrthonormalBasis of it (sampling.metal:158-171), general = 1 */
+#define RT_LIGHT_GENERAL 11
+#define RT_LIGHT_NORMAL  16
+#define RT_LIGHT_TANGENT 20
+#define RT_LIGHT_BITANGENT 24
 #define RT_LAYOUT_LIGHT_EXTENT 1u
+#define RT_LAYOUT_LIGHT_NORMALS 2u   /* a float4-per-light normal table is bound at RT_INDEX_LIGHT_NORMALS */
 #define RT_MAX_GROUPS     4   /* cullable object groups (16 sort keys)                                 */
 #define RT_GRP_K          0
 #define RT_GRP_ALWAYS     1

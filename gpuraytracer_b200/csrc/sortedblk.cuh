@@ -30,7 +30,7 @@ struct SortBlkSmem {
     static_assert(WORDS == (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + OFFS + 2u * RT_SORT_KEYS + 4u, "layout below");
 };
 
-template <int R, bool PERSIST, bool SPATIAL = false>
+template <int R, bool PERSIST, bool SPATIAL = false, bool MIS = false>
 __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                          float4 *__restrict__ out, const RTLaunchParams p,
                                                          const RTSceneLayout lay, float *sm, const RTTileSched ts,
@@ -216,6 +216,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
 #pragma unroll 1
         for (uint32_t b = 0; b < nb && count; b++) {
             const bool cont = b + 1 < nb;
+            const bool traceC = MIS || cont;        /* MIS (mis.cuh): the continuation ray is traced after the last bounce too */
             const bool sort = count > 32u;          /* one chunk: nothing to sort, the hit list is the order */
 
             /* -- A. shade set-up, the two rays of the bounce, the key: chunk c of the hit list by warp c % 4 -- */
@@ -253,7 +254,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     const float wx = h4.x, wy = h4.y;                                           /* :72-73 */
                     color = color * diffuse;                                                    /* :76 */
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
-                    if (cont) {
+                    if (traceC) {
                         const f3 right = mk(sh[(RT_SH_RX + 0) * lay.Tp], sh[(RT_SH_RX + 1) * lay.Tp], sh[(RT_SH_RX + 2) * lay.Tp]);
                         const f3 fwd = mk(sh[(RT_SH_FX + 0) * lay.Tp], sh[(RT_SH_FX + 1) * lay.Tp], sh[(RT_SH_FX + 2) * lay.Tp]);
                         const float ux = h4.z, uy = h4.w;                                       /* :93-94 */
@@ -270,11 +271,11 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                         const float *G = sm + lay.group + 4 + 8 * g;
                         const f3 w = mk(G[0], G[1], G[2]) - P, H = mk(G[4], G[5], G[6]);
                         bool clear = ray_clear_of_box(w, H, ld);
-                        if (cont) clear = clear && ray_clear_of_box(w, H, rd);
+                        if (traceC) clear = clear && ray_clear_of_box(w, H, rd);
                         if (!clear) key |= 1u << g;
                     }
                     SF(0, slot) = P.x; SF(1, slot) = P.y; SF(2, slot) = P.z;
-                    if (cont) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
+                    if (traceC) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
                     SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
                     SF(9, slot) = sp.x; SF(10, slot) = sp.z;
                     /* can the shadow ray skip the shell quads?  (rt_scene_layout.h; sorted.cuh: shadow_inside_shell) */
@@ -349,14 +350,14 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     float dist = 0.0f;
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
 #if RT_EXP_TRACE == 0
-                    if (cont) {
+                    if (traceC) {
                         rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = closest_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id);   /* :49 */
                     }
                     const bool shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);       /* :79-88 */
 #elif RT_EXP_TRACE == 1
                     bool shadowed;
-                    if (cont) {
+                    if (traceC) {
                         rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = dual_hit_pairs_masked(sc, pairs, pairsS, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
                     } else {
@@ -364,7 +365,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     }
 #else
                     bool shadowed;
-                    if (cont) {
+                    if (traceC) {
                         rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
                     } else {
@@ -376,17 +377,28 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                         const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
                         f3 lightColor = light_colour(mk(L[4], L[5], L[6]), inv, ldir);
                         lightColor = lightColor * saturate(dot(normal, ldir));
+                        if (MIS) lightColor = lightColor * misA_light_weight(L, P, normal, ldir);
                         const f3 lc = lightColor * mk(SF(6, slot), SF(7, slot), SF(8, slot));
                         res[0 * NSLOT + slot] = res[0 * NSLOT + slot] + lc.x;
                         res[1 * NSLOT + slot] = res[1 * NSLOT + slot] + lc.y;
                         res[2 * NSLOT + slot] = res[2 * NSLOT + slot] + lc.z;
                     }
+                    if (MIS) {      /* the cosine strategy's term for this continuation ray (one light on this path) */
+                        const float *sh = sm + lay.shade + surf;
+                        const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
+                        const f3 term = misA_cosine_term(L, P, normal, rd, hitC, dist, mk(SF(6, slot), SF(7, slot), SF(8, slot)));
+                        res[0 * NSLOT + slot] = res[0 * NSLOT + slot] + term.x;
+                        res[1 * NSLOT + slot] = res[1 * NSLOT + slot] + term.y;
+                        res[2 * NSLOT + slot] = res[2 * NSLOT + slot] + term.z;
+                    }
                     if (hitC) {
                         const float *sh = sm + lay.shade + id;
-                        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                  /* :59 */
-                            res[0 * NSLOT + slot] = sh[(RT_SH_ER + 0) * lay.Tp]; res[1 * NSLOT + slot] = sh[(RT_SH_ER + 1) * lay.Tp];
-                            res[2 * NSLOT + slot] = sh[(RT_SH_ER + 2) * lay.Tp];
-                        } else {
+                        if (sh[RT_SH_FLAG * lay.Tp] != 0.0f) {                                  /* :59; MIS: the path ends, nothing is assigned */
+                            if (!MIS) {
+                                res[0 * NSLOT + slot] = sh[(RT_SH_ER + 0) * lay.Tp]; res[1 * NSLOT + slot] = sh[(RT_SH_ER + 1) * lay.Tp];
+                                res[2 * NSLOT + slot] = sh[(RT_SH_ER + 2) * lay.Tp];
+                            }
+                        } else if (cont) {
                             alive = true;
                             const f3 hp = P + rd * dist;
                             SF(0, slot) = hp.x; SF(1, slot) = hp.y; SF(2, slot) = hp.z;

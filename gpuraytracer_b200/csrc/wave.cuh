@@ -92,7 +92,7 @@ struct WaveSmem {
     static constexpr uint32_t WORDS_PER_WARP = rtWaveWordsPerWarp(R);
 };
 
-template <bool COUNT, int UNROLL, int R, bool PERSIST, bool SPATIAL>
+template <bool COUNT, int UNROLL, int R, bool PERSIST, bool SPATIAL, bool MIS = false>
 __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ scene, const uint32_t *__restrict__ offsets,
                                                     float4 *__restrict__ out, const RTLaunchParams p,
                                                     const RTSceneLayout lay, float *sm,
@@ -307,8 +307,10 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     /* the continuation ray starts at the same point as the shadow ray: it is sampled first
                      * and traced together with the first light's shadow ray (dual_hit) */
                     const bool cont = b + 1 < nb;                                               /* warp-uniform */
+                    /* MIS (mis.cuh): the continuation ray is traced after the last bounce too, for its cosine-strategy term */
+                    const bool traceC = MIS || cont;
                     f3 rd = mk(0.0f, 0.0f, 0.0f);
-                    if (cont) {
+                    if (traceC) {
                         const float ux = h4.z, uy = h4.w;                                       /* :93-94 */
                         f3 sdir = sample_cosine_hemisphere(ux, uy);
                         rd = (right * sdir.x + normal * sdir.y) + fwd * sdir.z;                 /* sampling.metal:65 */
@@ -323,12 +325,13 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                         f3 ldir; float ldist;
                         f3 lightColor = sample_area_light(L, wx, wy, P, ldir, ldist);
                         lightColor = lightColor * saturate(dot(normal, ldir));                  /* :75 */
+                        if (MIS) lightColor = lightColor * misA_light_weight(L, P, normal, ldir);
                         bool shadowed;
                         if (paired) {                                                           /* warp-uniform, per launch */
-                            if (cont) hitC = dual_hit<false, UNROLL, true>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
+                            if (traceC) hitC = dual_hit<false, UNROLL, true>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
                             else shadowed = any_hit<false, UNROLL, true>(sc, P, ldir, 0.0f, ldist - 1e-3f);
                         } else {
-                            if (cont) hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
+                            if (traceC) hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ldist - 1e-3f, shadowed);
                             else shadowed = any_hit<false, UNROLL>(sc, P, ldir, 0.0f, ldist - 1e-3f);
                         }
                         if (!shadowed) acc = acc + lightColor * color;                          /* :88 */
@@ -336,7 +339,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                         uint32_t l = 0;
                         while (l < numLights) {
                             const uint32_t left = numLights - l;
-                            const uint32_t n = (cont && l == 0) ? 1u : (left >= 3u ? 3u : left);
+                            const uint32_t n = (traceC && l == 0) ? 1u : (left >= 3u ? 3u : left);
                             f3 ldir[3], lcol[3]; float ltmax[3]; bool shd[3] = { false, false, false };
 #pragma unroll
                             for (uint32_t r = 0; r < 3; r++) {
@@ -346,10 +349,11 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                     float ldist;
                                     lcol[r] = sample_area_light(L, wx, wy, P, ldir[r], ldist);
                                     lcol[r] = lcol[r] * saturate(dot(normal, ldir[r]));             /* :75 */
+                                    if (MIS) lcol[r] = lcol[r] * misA_light_weight(L, P, normal, ldir[r]);
                                     ltmax[r] = ldist - 1e-3f;
                                 }
                             }
-                            if (cont && l == 0) {
+                            if (traceC && l == 0) {
                                 hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);   /* + :49 */
                             } else if (n == 3) {
                                 any_hit_multi<false, 2, 3>(sc, P, ldir, ltmax, shd);
@@ -366,13 +370,18 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                             l += n;
                         }
                     }
+                    if (MIS) {      /* the cosine strategy's term of every light for this continuation ray, in light order */
+                        for (uint32_t l = 0; l < numLights; l++)
+                            acc = acc + misA_cosine_term(sm + lay.light + RT_LIGHT_WORDS * l, P, normal, rd, hitC, dist, color);
+                    }
                     if (hitC) {
                         const bool tri = id < lay.T;
                         const float *sh = tri ? sm + lay.shade + id : sm + lay.sshade + (id - lay.T);
                         const uint32_t stride = tri ? lay.Tp : lay.Sp;
                         const uint32_t fl = tri ? RT_SH_FLAG : RT_SSH_FLAG, er = tri ? RT_SH_ER : RT_SSH_ER;
-                        if (sh[fl * stride] != 0.0f) acc = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);   /* :59 */
-                        else { alive = true; hp = P + rd * dist; }
+                        if (sh[fl * stride] != 0.0f) {                                          /* :59; MIS: the path ends, nothing is assigned */
+                            if (!MIS) acc = mk(sh[(er + 0) * stride], sh[(er + 1) * stride], sh[(er + 2) * stride]);
+                        } else if (cont) { alive = true; hp = P + rd * dist; }
                     }
                 }
                 const uint32_t mask = __ballot_sync(0xffffffffu, alive);

@@ -50,6 +50,17 @@ class Renderer:
         self.accel = accel
         self.last_command = None
         self.debug_buffer = None
+        self.light_normals_buffer = None
+
+    def set_light_normals(self, normals):
+        """Bind a per-light normal table (float32 [L, 4], xyz = normal) at RT_INDEX_LIGHT_NORMALS, or None to go back to
+        the reference's literal (0,-1,0) (sampling.metal:205).  SURVEY N3."""
+        if normals is None:
+            self.light_normals_buffer = None
+            return
+        n = np.ascontiguousarray(normals, np.float32).reshape(-1, 4)
+        assert n.shape[0] == self.scene.num_lights
+        self.light_normals_buffer = self.device.make_buffer(n)
 
     def params(self, **over):
         p = default_params(self.width, self.height, row0=self.row0, rows=self.rows,
@@ -69,6 +80,8 @@ class Renderer:
         check(lib.rtSetAccelerationStructure(cmd.h, self.accel, L.INDEX_ACCEL), "rtSetAccelerationStructure")
         if self.spheres_buffer is not None:
             cmd.set_buffer(self.spheres_buffer, 0, L.INDEX_SPHERES)
+        if self.light_normals_buffer is not None:
+            cmd.set_buffer(self.light_normals_buffer, 0, L.INDEX_LIGHT_NORMALS)
         cmd.set_buffer(self.render_buffer, 0, L.INDEX_OUTPUT)          # setTexture(renderTexture, 0)
         cmd.set_buffer(self.random_buffer, 0, L.INDEX_OFFSETS)         # setTexture(randomTexture, 1)
         params = self.params(**over)

@@ -69,6 +69,9 @@ enum {
     RT_INDEX_ACCEL     = 5,    /* acceleration structure                        */
     RT_INDEX_DEBUG     = 6,    /* pathTrace: bound, never written; drawTriangle: float3 text buffer */
     RT_INDEX_SPHERES   = 7,    /* extension (config 4): SphereGPU[S]            */
+    RT_INDEX_LIGHT_NORMALS = 8, /* extension, optional: float4[L], xyz = the light's normal (normalised by
+                                  the library); unbound = the reference's literal (0,-1,0), sampling.metal:205.
+                                  A side table, so that SquareLightGPU keeps the reference's layout */
     RT_INDEX_OUTPUT    = 16,   /* texture(0) of pathTrace: float4 per pixel     */
     RT_INDEX_OFFSETS   = 17,   /* texture(1) of pathTrace: uint32 per pixel     */
     RT_INDEX_COUNT     = 18
@@ -97,9 +100,16 @@ enum { RT_FORMAT_RGBA32_FLOAT = 1, RT_FORMAT_R32_UINT = 2 };
  * the table says.  Flags above the low byte: COUNT_RAYS (below); LIGHT_EXTENT: sampleAreaLight takes its sample over the
  * light's own width x depth, right = (width/2,0,0), up = (0,0,depth/2), instead of the 0.5 x 0.5 the reference hard-codes
  * (sampling.metal:207-209, the TODO SURVEY N3 names); off = the reference's literals.  Every kernel form honours it, the
- * image changes with it (the oracle takes the same flag). */
+ * image changes with it (the oracle takes the same flag).
+ * MIS (the reference's own TODO, the commented-out block of sampling.metal:238-260 that mode B carries out):
+ * the direct light of every shaded bounce is estimated by the light sample AND by the cosine-sampled continuation ray,
+ * combined with the balance heuristic (powerHeuristic, beta = 1, over calculateSquareLightPdf and
+ * calculateCosineWeightedPdf: shaders.metal:132-137, 315-326, 376-380).  Same expectation as the flag-off light term,
+ * lower variance near the light; the continuation ray is then traced after the last bounce too, and an emissive hit
+ * after a shaded bounce ends the path without raytrace.metal:59's `accumulated = emissive` (oracle/rt_oracle.c states
+ * the estimator).  Forms: SMEM, WAVE, SORTED_BLOCK, BVH; the others fall back to those.  Not with COUNT_RAYS. */
 enum { RT_VARIANT_DEFAULT = 0, RT_VARIANT_SMEM = 1, RT_VARIANT_CONST = 2, RT_VARIANT_WAVE = 3, RT_VARIANT_TILES = 16, RT_VARIANT_WIDE = 17, RT_VARIANT_SORTED = 18, RT_VARIANT_SORTED_TILES = 19, RT_VARIANT_SORTED_BLOCK = 20, RT_VARIANT_SORTED_BLOCK_TILES = 21, RT_VARIANT_BVH = 22,
-       RT_VARIANT_COUNT_RAYS = 0x100, RT_VARIANT_LIGHT_EXTENT = 0x200 };
+       RT_VARIANT_COUNT_RAYS = 0x100, RT_VARIANT_LIGHT_EXTENT = 0x200, RT_VARIANT_MIS = 0x400 };
 
 /* What the reference hard-codes in the shader (raytrace.metal:24-25,
  * shaders.metal:644,648) plus the tile / progressive controls BASELINE.json's

@@ -126,24 +126,60 @@ static inline void camera_ray(const CameraGPU *camera, uint32_t ix, uint32_t iy,
     *direction = dir;
 }
 
-/* sampling.metal:198-236.  The 0.5 x 0.5 extent and the -y normal are the
- * reference's own literals (:207-209); light.width / light.depth are ignored --
- * unless the caller sets light_extent (RT_VARIANT_LIGHT_EXTENT, SURVEY N3: the
- * generalisation the TODO of :175 asks for, as directSquareLightRay :180-181 does
- * it in mode B), when right and up span the light's own width x depth. */
+/* ---- light geometry -------------------------------------------------------------------------------
+ * The reference hard-codes the light's normal (0,-1,0) and spans its sample rectangle with right = (0.25,0,0),
+ * up = (0,0,0.25) (sampling.metal:205-209; the TODO of :175 asks for the generalisation).  Extensions, inert unless asked for:
+ *   RT_VARIANT_LIGHT_EXTENT   right / up span the light's own width x depth (half extents width/2, depth/2)
+ *   a per-light NORMAL table  (rt_oracle_set_light_normals; the library: a buffer bound at RT_INDEX_LIGHT_NORMALS, float4
+ *                             per light): right = tangent * hx, up = bitangent * hz with buildOrthonormalBasis(normal)
+ *                             (sampling.metal:158-171), as directSquareLightRay (:173-196) builds its rectangle.  For
+ *                             (0,-1,0) that basis is (1,0,0), (0,0,1): the reference's literals.
+ * Without a table the literals themselves are used, so the reference's bits cannot move. */
+static const float *g_light_normals = 0;
+void rt_oracle_set_light_normals(const float *normals_float4_per_light) { g_light_normals = normals_float4_per_light; }
+
+typedef struct { f3 center, normal, tangent, bitangent, right, up; float hx, hz; } light_geom;
+
+/* sampling.metal:158-171 */
+static inline void build_orthonormal_basis(f3 normal, f3 *tangent, f3 *bitangent) {
+    f3 t;
+    if (fabsf(normal.x) > 0.9f) t = f3_normalize(f3_sub(f3_make(0, 1, 0), f3_scale(normal, f3_dot(f3_make(0, 1, 0), normal))));
+    else                        t = f3_normalize(f3_sub(f3_make(1, 0, 0), f3_scale(normal, f3_dot(f3_make(1, 0, 0), normal))));
+    *tangent = t;
+    *bitangent = f3_cross(normal, t);
+}
+
+static inline light_geom light_geometry(const SquareLightGPU *light, uint32_t l, int light_extent) {
+    light_geom g;
+    g.center = f3_ld(&light->center);
+    g.hx = light_extent ? 0.5f * light->width : 0.25f;
+    g.hz = light_extent ? 0.5f * light->depth : 0.25f;
+    if (g_light_normals) {
+        g.normal = f3_normalize(f3_make(g_light_normals[4 * l], g_light_normals[4 * l + 1], g_light_normals[4 * l + 2]));
+        build_orthonormal_basis(g.normal, &g.tangent, &g.bitangent);
+        g.right = f3_scale(g.tangent, g.hx);
+        g.up = f3_scale(g.bitangent, g.hz);
+    } else {
+        g.normal = f3_make(0.0f, -1.0f, 0.0f);
+        g.tangent = f3_make(1.0f, 0.0f, 0.0f);
+        g.bitangent = f3_make(0.0f, 0.0f, 1.0f);
+        g.right = f3_make(g.hx, 0.0f, 0.0f);
+        g.up = f3_make(0.0f, 0.0f, g.hz);
+    }
+    return g;
+}
+
 /* Test hook: the light sample point of the calling thread's last sample_area_light (rt_groups.c restates the sorted
  * kernel's culling rules, one of which looks at the shadow ray's far end). */
 _Thread_local float rt_oracle_light_sample[3];
 
-static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float uy, f3 position,
-                                   f3 *lightDirection, float *lightDistance, int light_extent) {
+/* sampling.metal:198-236 over the geometry above */
+static inline f3 sample_area_light(const SquareLightGPU *light, const light_geom *g, float ux, float uy, f3 position,
+                                   f3 *lightDirection, float *lightDistance) {
     ux = ux * 2.0f - 1.0f;
     uy = uy * 2.0f - 1.0f;
 
-    f3 normal = f3_make(0.0f, -1.0f, 0.0f);
-    f3 right = f3_make(light_extent ? 0.5f * light->width : 0.25f, 0.0f, 0.0f);
-    f3 up = f3_make(0.0f, 0.0f, light_extent ? 0.5f * light->depth : 0.25f);
-    f3 samplePosition = f3_add(f3_add(f3_ld(&light->center), f3_scale(right, ux)), f3_scale(up, uy));
+    f3 samplePosition = f3_add(f3_add(g->center, f3_scale(g->right, ux)), f3_scale(g->up, uy));
 
     rt_oracle_light_sample[0] = samplePosition.x; rt_oracle_light_sample[1] = samplePosition.y; rt_oracle_light_sample[2] = samplePosition.z;
     f3 ld = f3_sub(samplePosition, position);
@@ -153,11 +189,67 @@ static inline f3 sample_area_light(const SquareLightGPU *light, float ux, float 
 
     f3 lightColor = f3_make(light->color.x, light->color.y, light->color.z);
     lightColor = f3_scale(lightColor, inverseLightDistance * inverseLightDistance);
-    lightColor = f3_scale(lightColor, rt_saturate(f3_dot(f3_neg(ld), normal)));
+    lightColor = f3_scale(lightColor, rt_saturate(f3_dot(f3_neg(ld), g->normal)));
 
     *lightDirection = ld;
     *lightDistance = dist;
     return lightColor;
+}
+
+/* ---- multiple importance sampling in mode A (RT_VARIANT_MIS) ---------------------------------------------
+ * The reference's pathTrace has no MIS weights (its own TODO: the commented-out block of sampling.metal:238-260, which
+ * mode B carries out).  With the flag, the direct light of every shaded bounce is estimated by TWO strategies
+ * combined with the balance heuristic -- powerHeuristic with beta = 1 (shaders.metal:132-137), over
+ * calculateSquareLightPdf (:315-326, with the light's normal) and calculateCosineWeightedPdf (:376-380):
+ *   light strategy   the reference's own sample (sampleAreaLight + shadow ray), its term g = lightColor * color weighted
+ *                    by w_l = heuristic(p_light, p_cosine)
+ *   cosine strategy  the continuation ray the kernel samples anyway (cosine-weighted): when it passes through the light's
+ *                    sample rectangle, front side, with nothing nearer than the rectangle minus 1e-3 (the shadow ray's
+ *                    own visibility rule), it adds  light.color * (pi / A_s) * color * w_c,  A_s = the rectangle's area,
+ *                    w_c = heuristic(p_cosine, p_light)
+ * Both estimate  (light.color * color / A_s) * integral over the rectangle's solid angle of cos(theta_surface) V dw:
+ * the light strategy because dA cos(theta_light) / d^2 = dw, the cosine strategy because its pdf is cos(theta_surface) / pi.
+ * The weights add up to one (up to the heuristic's 1e-6), so the expectation is the flag-off light term's.
+ * Two things change with the flag, both needed for that: the continuation ray is traced after the LAST bounce too (for
+ * its cosine term only), and an emissive hit after a shaded bounce ends the path WITHOUT `accumulated = emissive`
+ * (raytrace.metal:59 discards the light gathered so far; a camera ray that sees the light still takes its emissive).
+ * Checker-only selectors (the library has no such forms): RT_ORACLE_MIS_LIGHT_ONLY w_l = 1, w_c = 0;
+ * RT_ORACLE_MIS_COSINE_ONLY w_l = 0, w_c = 1 -- same expectation, which tests/test_mis_cpu.py checks statistically. */
+static inline float mis_heuristic(float pdf1, float pdf2, float pdf3) {
+    const float n = 1.0f;                       /* samplesPerStrategy = 1; pow(x, 1.0) = x */
+    float p1 = n * pdf1;
+    float sum = p1 + n * pdf2 + n * pdf3;
+    return p1 / (sum + 1e-6f);
+}
+static inline float mis_square_light_pdf(f3 origin, const SquareLightGPU *light, const light_geom *g, f3 direction) {
+    f3 toLight = f3_sub(g->center, origin);
+    float distance = f3_length(toLight);
+    float cosTheta = fmaxf(0.0f, f3_dot(f3_neg(direction), g->normal));
+    float area = light->width * light->depth;
+    return (distance * distance) / (area * cosTheta + 1e-6f);
+}
+static inline float mis_cosine_pdf(f3 normal, f3 direction) {
+    return fmaxf(0.0f, f3_dot(normal, direction)) / 3.14159265358979323846264338327950288f;
+}
+/* the cosine strategy's term of one light for the continuation ray (P, rd) whose closest hit is (hit, hitDistance) */
+static inline f3 mis_cosine_term(const SquareLightGPU *light, const light_geom *g, f3 P, f3 normal, f3 rd,
+                                 int hit, float hitDistance, f3 color, int mode) {
+    const f3 zero = f3_make(0.0f, 0.0f, 0.0f);
+    if (mode == 2) return zero;                                        /* light strategy alone */
+    float denom = f3_dot(rd, g->normal);
+    if (!(denom < 0.0f)) return zero;                                  /* the rectangle's front side faces -normal */
+    float t = f3_dot(f3_sub(g->center, P), g->normal) / denom;
+    if (!(t > 0.0f)) return zero;
+    if (hit && hitDistance < t - 1e-3f) return zero;                   /* something nearer: raytrace.metal:81's rule */
+    f3 v = f3_sub(f3_add(P, f3_scale(rd, t)), g->center);
+    if (!(fabsf(f3_dot(v, g->tangent)) <= g->hx && fabsf(f3_dot(v, g->bitangent)) <= g->hz)) return zero;
+    float weight = 1.0f;
+    if (mode == 1) weight = mis_heuristic(mis_cosine_pdf(normal, rd), mis_square_light_pdf(P, light, g, rd), 0.0f);
+    float area = (2.0f * g->hx) * (2.0f * g->hz);
+    f3 term = f3_make(light->color.x, light->color.y, light->color.z);
+    term = f3_scale(term, 3.14159265358979323846264338327950288f / area);
+    term = f3_scale(term, weight);
+    return f3_mul(term, color);
 }
 
 typedef struct {
@@ -169,6 +261,7 @@ typedef struct {
     uint32_t T, S, L;
     int bounces;
     int light_extent;
+    int mis;          /* 0 off, 1 RT_VARIANT_MIS, 2 / 3 the checker-only single-strategy selectors */
 } scene_view;
 
 /* Test hook (rt_groups.c: the group-culling checker sees every ray query of a frame and its answer); NULL otherwise. */
@@ -196,16 +289,17 @@ static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint
     f3 accumulatedColor = f3_make(0.0f, 0.0f, 0.0f);
     f3 color = f3_make(1.0f, 1.0f, 1.0f);
 
+    cnt[RT_CNT_CLOSEST_RAYS]++;
+    rt_hit hit = scene_intersect(sc, ro, rd, rmin, rmax, 0);
     for (int bounce = 0; bounce < sc->bounces; bounce++) {
-        cnt[RT_CNT_CLOSEST_RAYS]++;
-        rt_hit hit = scene_intersect(sc, ro, rd, rmin, rmax, 0);
         if (!hit.hit) break;
 
         /* materials[primitive_id]; sphere primitives (extension) carry their own */
         const MaterialGPU *m = hit.primitive_id < sc->T ? &sc->materials[hit.primitive_id]
                                                         : &sc->spheres[hit.primitive_id - sc->T].material;
         if (f3_length(f3_ld(&m->emissive)) > 0.0f) {
-            accumulatedColor = f3_ld(&m->emissive);      /* assignment, raytrace.metal:59 */
+            /* assignment, raytrace.metal:59.  MIS: only a camera ray takes the emissive (see above) */
+            if (!sc->mis || bounce == 0) accumulatedColor = f3_ld(&m->emissive);
             break;
         }
         cnt[RT_CNT_SHADED_BOUNCES]++;
@@ -226,9 +320,15 @@ static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint
         /* reference: lights[0] only (raytrace.metal:22); extension: every light,
          * same w, one shadow ray each, summed in index order */
         for (uint32_t l = 0; l < sc->L; l++) {
+            const light_geom g = light_geometry(&sc->lights[l], l, sc->light_extent);
             f3 ldir; float ldist;
-            f3 lightColor = sample_area_light(&sc->lights[l], wx, wy, P, &ldir, &ldist, sc->light_extent);
+            f3 lightColor = sample_area_light(&sc->lights[l], &g, wx, wy, P, &ldir, &ldist);
             lightColor = f3_scale(lightColor, rt_saturate(f3_dot(normal, ldir)));
+            if (sc->mis) {
+                float weight = sc->mis == 1 ? mis_heuristic(mis_square_light_pdf(P, &sc->lights[l], &g, ldir), mis_cosine_pdf(normal, ldir), 0.0f)
+                                            : (sc->mis == 2 ? 1.0f : 0.0f);
+                lightColor = f3_scale(lightColor, weight);
+            }
             /* default-constructed ray: min_distance = 0 (raytrace.metal:79-82) */
             cnt[RT_CNT_SHADOW_RAYS]++;
             rt_hit sh = scene_intersect(sc, P, ldir, 0.0f, ldist - 1e-3f, 1);
@@ -241,6 +341,18 @@ static inline f3 trace_path(const scene_view *sc, uint32_t ix, uint32_t iy, uint
         sd = align_hemisphere(sd, normal);
         ro = P;
         rd = sd;
+        /* the next bounce's closest hit (raytrace.metal:49 at the top of the reference's loop); MIS: after the last
+         * bounce too, for the cosine strategy's term */
+        if (bounce + 1 < sc->bounces || sc->mis) {
+            cnt[RT_CNT_CLOSEST_RAYS]++;
+            hit = scene_intersect(sc, ro, rd, rmin, rmax, 0);
+            if (sc->mis)
+                for (uint32_t l = 0; l < sc->L; l++) {
+                    const light_geom g = light_geometry(&sc->lights[l], l, sc->light_extent);
+                    accumulatedColor = f3_add(accumulatedColor, mis_cosine_term(&sc->lights[l], &g, P, normal, rd, hit.hit,
+                                                                                 hit.distance, color, sc->mis));
+                }
+        }
     }
     cnt[RT_CNT_PATHS]++;
     return accumulatedColor;
@@ -267,7 +379,8 @@ int rt_oracle_pathtrace(const CameraGPU *cameras, const MaterialGPU *materials,
 
     scene_view sc = { cameras, materials, lights, vertices, spheres,
                       p->numTriangles, p->numSpheres, p->numLights, p->bounces,
-                      (p->variant & RT_VARIANT_LIGHT_EXTENT) != 0 };
+                      (p->variant & RT_VARIANT_LIGHT_EXTENT) != 0,
+                      (p->variant & RT_ORACLE_MIS_LIGHT_ONLY) ? 2 : (p->variant & RT_ORACLE_MIS_COSINE_ONLY) ? 3 : (p->variant & RT_VARIANT_MIS) ? 1 : 0 };
     uint64_t total[RT_CNT_COUNT] = { 0 };
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
@@ -326,7 +439,8 @@ void rt_oracle_camera_ray(const CameraGPU *cam, uint32_t x, uint32_t y, float jx
 void rt_oracle_sample_area_light(const SquareLightGPU *light, float ux, float uy, const float pos[3],
                                  float color[3], float ldir[3], float *ldist) {
     f3 d; float dist;
-    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist, 0);
+    const light_geom g = light_geometry(light, 0, 0);
+    f3 c = sample_area_light(light, &g, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist);
     color[0] = c.x; color[1] = c.y; color[2] = c.z;
     ldir[0] = d.x; ldir[1] = d.y; ldir[2] = d.z;
     *ldist = dist;
@@ -335,7 +449,8 @@ void rt_oracle_sample_area_light(const SquareLightGPU *light, float ux, float uy
 void rt_oracle_sample_area_light_ex(const SquareLightGPU *light, float ux, float uy, const float pos[3],
                                     float color[3], float ldir[3], float *ldist, int light_extent) {
     f3 d; float dist;
-    f3 c = sample_area_light(light, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist, light_extent);
+    const light_geom g = light_geometry(light, 0, light_extent);      /* (light 0's row of the normal table, if one is set) */
+    f3 c = sample_area_light(light, &g, ux, uy, f3_make(pos[0], pos[1], pos[2]), &d, &dist);
     color[0] = c.x; color[1] = c.y; color[2] = c.z;
     ldir[0] = d.x; ldir[1] = d.y; ldir[2] = d.z;
     *ldist = dist;

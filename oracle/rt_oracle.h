@@ -52,6 +52,13 @@ int rt_oracle_drawtriangle(const CameraGPU *cameras, const MaterialGPU *material
 
 /* Pieces exported for known-answer tests. */
 float    rt_oracle_halton(uint32_t i, uint32_t d);            /* sampling.metal:107-122 */
+/* Checker-only selectors in RTLaunchParams.variant beside RT_VARIANT_MIS (rt_oracle.c: "multiple importance sampling in
+ * mode A"): the two strategies alone, each with weight one.  The library has no such forms. */
+#define RT_ORACLE_MIS_LIGHT_ONLY  0x0800u
+#define RT_ORACLE_MIS_COSINE_ONLY 0x1000u
+/* per-light normals (float4 per light; NULL = the reference's (0,-1,0) literals): what the library takes as a buffer
+ * bound at RT_INDEX_LIGHT_NORMALS.  A process-wide setting of the checker: set, trace, reset. */
+void     rt_oracle_set_light_normals(const float *normals_float4_per_light);
 uint32_t rt_oracle_hash(uint32_t x);                          /* sampling.metal:68-75   */
 void     rt_oracle_camera_ray(const CameraGPU *cam, uint32_t x, uint32_t y, float jx, float jy,
                               float origin[3], float dir[3]); /* sampling.metal:125-157 */

@@ -26,6 +26,8 @@ lib.rt_oracle_halton.argtypes = [C.c_uint32, C.c_uint32]
 lib.rt_oracle_hash.restype = C.c_uint32
 lib.rt_oracle_hash.argtypes = [C.c_uint32]
 lib.rt_oracle_max_threads.restype = C.c_int
+lib.rt_oracle_set_light_normals.restype = None
+lib.rt_oracle_set_light_normals.argtypes = [C.c_void_p]
 
 
 def vp(a):
@@ -52,9 +54,14 @@ def offsets(width, row0, rows, seed=1):
     return off
 
 
+MIS, MIS_LIGHT_ONLY, MIS_COSINE_ONLY = 0x400, 0x400 | 0x800, 0x400 | 0x1000      # RT_VARIANT_MIS; the checker-only selectors
+
+
 def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, bounces=3, accumulate=False,
-              out=None, off=None, seed=1, nthreads=0, tile_rows=0, tile_stride=0, light_extent=False):
-    """Returns (image float32 [rows,width,4], counters uint64[8]).  light_extent: RT_VARIANT_LIGHT_EXTENT (0x200)."""
+              out=None, off=None, seed=1, nthreads=0, tile_rows=0, tile_stride=0, light_extent=False, mis=0,
+              light_normals=None):
+    """Returns (image float32 [rows,width,4], counters uint64[8]).  light_extent: RT_VARIANT_LIGHT_EXTENT (0x200);
+    mis: 0, MIS, MIS_LIGHT_ONLY or MIS_COSINE_ONLY; light_normals: float32 [L, 4] or None (the reference's (0,-1,0))."""
     rows = height - row0 if rows is None else rows
     if off is None:
         off = offsets(width, row0, rows, seed)
@@ -62,10 +69,15 @@ def pathtrace(scene, width, height, spp, *, row0=0, rows=None, first_sample=0, b
         out = np.zeros((rows, width, 4), np.float32)
     cnt = np.zeros(8, np.uint64)
     p = RTLaunchParams(width, height, row0, rows, spp, first_sample, bounces, int(accumulate),
-                       scene["T"], scene["S"], scene["L"], 6, 300, 0x200 if light_extent else 0, tile_rows, tile_stride)
-    rc = lib.rt_oracle_pathtrace(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
-                                 vp(scene["vertices"]), vp(scene["spheres"]), vp(off), vp(out), C.byref(p),
-                                 vp(cnt), nthreads)
+                       scene["T"], scene["S"], scene["L"], 6, 300, (0x200 if light_extent else 0) | int(mis), tile_rows, tile_stride)
+    normals = None if light_normals is None else np.ascontiguousarray(light_normals, np.float32).reshape(-1, 4)
+    lib.rt_oracle_set_light_normals(vp(normals))
+    try:
+        rc = lib.rt_oracle_pathtrace(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]),
+                                     vp(scene["vertices"]), vp(scene["spheres"]), vp(off), vp(out), C.byref(p),
+                                     vp(cnt), nthreads)
+    finally:
+        lib.rt_oracle_set_light_normals(None)
     if rc != 0:
         raise RuntimeError(f"rt_oracle_pathtrace returned {rc}")
     return out, cnt
