@@ -332,13 +332,19 @@ def run_ours(a, rank, world, local_rank):
         fp32_peak = r.device.measure_fp32_peak()
     host_img = torch.empty((H, W, local.shape[2]), dtype=torch.float32).pin_memory() if rank == 0 else None
 
+    gather_ev = []                                       # (start, end) CUDA events around this rank's part of the gather
+
     def step(e2e):
         if e2e:   # host -> device: scene + this rank's offsets, from the buffers' pinned mirrors
             for b in upload:
                 b.did_modify()
         cmds = launch()
         with torch.cuda.stream(stream):
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record(stream)
             full = D.gather_rows(local, H, world, rank, TILE_ROWS)
+            g1.record(stream)
+            gather_ev.append((g0, g1))
             if e2e and rank == 0:
                 host_img.copy_(full, non_blocking=True)
         return cmds, full
@@ -366,6 +372,14 @@ def run_ours(a, rank, world, local_rank):
     t_wall1 = time.time()
     ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
     kernel_ms = sum(c.gpu_time_ms() for c in cmds) / a.steps      # this rank's prep + trace per step
+    # where a multi-GPU step goes: every rank's kernel time, and the time between a rank's kernel end and the end of its
+    # part of the gather (on rank 0 that includes waiting for the slowest rank)
+    gather_ms = sum(g0.elapsed_time(g1) for g0, g1 in gather_ev[-a.steps:]) / a.steps
+    per_rank = torch.zeros(2 * world, dtype=torch.float64, device=dev)
+    per_rank[2 * rank], per_rank[2 * rank + 1] = kernel_ms, gather_ms
+    if world > 1:
+        dist.all_reduce(per_rank)
+    per_rank = per_rank.tolist()
     launches = sum(c.launch_count() for c in cmds)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -414,7 +428,10 @@ def run_ours(a, rank, world, local_rank):
            "clocks": clk,
            "e2e": {"value": frame_paths * a.steps / e2e_s / 1e6, "unit": UNIT,
                    "h2d_bytes_per_step": int(h2d_t.item()), "d2h_bytes_per_step": W * H * 4 * local.shape[2]},
-           "gpu_launches": launches * world}
+           "gpu_launches": launches * world,
+           "ranks": {"kernel_ms": [round(v, 3) for v in per_rank[0::2]], "gather_ms": [round(v, 3) for v in per_rank[1::2]],
+                     "note": "per rank and step: prep + trace (CUDA events of the commands); kernel end -> end of the rank's part of the "
+                             "gather (rank 0: receive from every rank + index_select into place; includes waiting for the slowest rank)"}}
     nc = ncu_constants()
     headline = not a.modeb and a.scene == "cornell" and (W, H, a.bounces, a.frames) == (1920, 1080, 3, 1)
     if flops is not None:

@@ -40,19 +40,35 @@ def scatter_index(height, world, tile_rows=8):
     return idx, pad
 
 
+_GATHER_CACHE = {}
+
+
 def gather_rows(local, height, world, rank, tile_rows=8, group=None):
     """local: torch tensor [pad, W, C] (this rank's rows first, padding after).
-    Returns the full [height, W, C] image on rank 0, None elsewhere."""
+    Returns the full [height, W, C] image on rank 0, None elsewhere.
+
+    Rank 0 keeps, per image shape, the rank-major receive buffer, the row index on the device and the output image, so a
+    step allocates nothing and moves every row twice (NCCL receive into the rank-major buffer, one index_select into
+    place): the gather lists VIEWS of the receive buffer, there is no concatenation.  The returned image is reused by
+    the next call of the same shape."""
     import torch
     import torch.distributed as dist
     if world == 1:
         return local[:height]
-    idx, pad = scatter_index(height, world, tile_rows)
-    assert local.shape[0] == pad
-    if rank == 0:
-        parts = [torch.empty_like(local) for _ in range(world)]
-        dist.gather(local, parts, dst=0, group=group)
-        allrows = torch.cat(parts, 0)
-        return allrows.index_select(0, torch.as_tensor(idx, device=local.device))
-    dist.gather(local, None, dst=0, group=group)
-    return None
+    if rank != 0:
+        dist.gather(local, None, dst=0, group=group)
+        return None
+    key = (tuple(local.shape), local.dtype, local.device, height, world, tile_rows)
+    c = _GATHER_CACHE.get(key)
+    if c is None:
+        idx, pad = scatter_index(height, world, tile_rows)
+        assert local.shape[0] == pad
+        allrows = torch.empty((world * pad,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        c = dict(allrows=allrows, parts=list(allrows.view((world, pad) + tuple(local.shape[1:])).unbind(0)),
+                 idx=torch.as_tensor(idx, device=local.device),
+                 full=torch.empty((height,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device))
+        _GATHER_CACHE.clear()                      # one shape at a time: these are frame-sized buffers
+        _GATHER_CACHE[key] = c
+    dist.gather(local, c["parts"], dst=0, group=group)
+    torch.index_select(c["allrows"], 0, c["idx"], out=c["full"])
+    return c["full"]
