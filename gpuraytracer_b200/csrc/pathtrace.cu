@@ -1182,6 +1182,7 @@ pathTrace_sortedblk_tiles6(const float *__restrict__ scene, const uint32_t *__re
 }
 
 #include "bvh.cuh"
+#include "bvh_build.cuh"
 
 #include "modeb.cuh"
 

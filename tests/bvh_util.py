@@ -26,3 +26,37 @@ def tessellate(vertices, materials, T, n):
                     k += 1
     assert k == T * n * n
     return out_v.reshape(-1).view(np.uint8).copy(), out_m.reshape(-1).copy(), k
+
+
+LEAF = 0x80000000
+
+
+def check_nodes(nodes, order, verts, T, max_leaf=12):
+    """Walks a hierarchy in the layout of csrc/host_bvh.h (nodes: uint32 [n, 16]) from inner node 0: every triangle is in
+    exactly one leaf, leaves hold at most max_leaf, and every box on the way down to a triangle contains it.
+    Returns (depth, leaves, mean triangles per leaf)."""
+    assert sorted(np.asarray(order).tolist()) == list(range(T))
+    v = verts.view(np.float32).reshape(T, 3, 4)[:, :, :3]
+    f = nodes.view(np.float32)
+    seen = np.zeros(T, bool)
+    stack = [(0, np.full(3, -np.inf, np.float32), np.full(3, np.inf, np.float32), 1)]
+    maxd, leaves = 0, 0
+    while stack:
+        ref, lo, hi, d = stack.pop()
+        maxd = max(maxd, d)
+        if ref & LEAF:
+            first, count = ref & 0x07ffffff, ((ref >> 27) & 15) + 1
+            assert count <= max_leaf
+            leaves += 1
+            ids = np.asarray(order[first:first + count])
+            assert not seen[ids].any()
+            seen[ids] = True
+            tri = v[ids]
+            assert np.all(tri >= lo) and np.all(tri <= hi), (first, count)
+            continue
+        nd, fd = nodes[ref], f[ref]
+        for lo_c, hi_c, r in ((fd[0:3], fd[4:7], int(nd[3])), (fd[8:11], fd[12:15], int(nd[7]))):
+            if np.all(lo_c <= hi_c):                       # (an empty box marks the unused child of a one-leaf tree)
+                stack.append((r, np.maximum(lo, lo_c), np.minimum(hi, hi_c), d + 1))
+    assert seen.all()
+    return maxd, leaves, T / max(leaves, 1)

@@ -27,7 +27,7 @@ for n in SIZES:
             os.environ["RT_BVH_LEAF"] = leaf
         r = G.Renderer(sc, W, H, device=dev)               # a new queue: a new hierarchy
         os.environ.pop("RT_BVH_FORM", None)
-        t0 = time.time(); r.draw(spp=2, variant=L.VARIANT_BVH); build_s = time.time() - t0     # includes the host build
+        t0 = time.time(); r.draw(spp=2, variant=L.VARIANT_BVH); build_s = time.time() - t0     # includes the device build
         if form == "-":
             os.environ.pop("RT_BVH_FORM", None)
         else:
@@ -41,7 +41,7 @@ for n in SIZES:
         if ref is None:
             ref = img
         line = (f"T = {sc.num_triangles:6d} {form:>4s} {('leaf ' + leaf) if leaf else ''}: {ms:8.2f} ms  {W * H * SPP / ms / 1e3:8.1f} Mpaths/s  "
-                f"(first draw incl. host build {build_s * 1e3:.0f} ms)  same image as the first form: {np.array_equal(img, ref)}")
+                f"(first draw incl. device build and Python {build_s * 1e3:.0f} ms)  same image as the first form: {np.array_equal(img, ref)}")
         print(line, flush=True)
     os.environ.pop("RT_BVH_FORM", None)
     if n == 1:
