@@ -20,7 +20,7 @@
     X(cuDevicePrimaryCtxRelease) X(cuCtxSetCurrent) X(cuCtxSynchronize) X(cuModuleLoadData) X(cuModuleUnload) \
     X(cuModuleGetFunction) X(cuModuleGetGlobal) X(cuFuncSetAttribute) X(cuMemAlloc) X(cuMemFree) \
     X(cuMemHostAlloc) X(cuMemHostGetDevicePointer) X(cuMemFreeHost) X(cuMemcpyHtoD) X(cuMemcpyDtoH) X(cuMemcpyHtoDAsync) \
-    X(cuMemcpyDtoHAsync) X(cuMemcpyDtoDAsync) X(cuMemsetD8) X(cuMemsetD8Async) X(cuStreamCreate) \
+    X(cuMemcpyDtoHAsync) X(cuMemcpyDtoDAsync) X(cuMemcpy2DAsync) X(cuCtxEnablePeerAccess) X(cuDeviceCanAccessPeer) X(cuMemsetD8) X(cuMemsetD8Async) X(cuStreamCreate) \
     X(cuStreamDestroy) X(cuStreamSynchronize) X(cuEventCreate) X(cuEventRecord) X(cuStreamWaitEvent) \
     X(cuEventSynchronize) X(cuEventElapsedTime) X(cuEventDestroy) X(cuLaunchKernel) \
     X(cuOccupancyMaxActiveBlocksPerMultiprocessor)

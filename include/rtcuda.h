@@ -275,12 +275,18 @@ int rtPathTraceNoAlloc(const void *camera, const void *materials, const void *li
                        const void *spheresOrNull, const uint32_t *offsets, float *out,
                        const RTLaunchParams *params, void *cuStream);
 
-/* ---- new: one process, several GPUs, row tiles ------------------------------ */
+/* ---- new: one process, several GPUs, row tiles (SURVEY 8b "Multi-GPU (new)", 8e) ----
+ * rtGroupCreate makes one device + queue per ordinal (an ordinal may repeat) and lets the members reach member 0's
+ * memory peer to peer where the hardware allows it. */
 int rtGroupCreate(const int *ordinals, int count, RTGroup **out);
 int rtGroupDeviceCount(RTGroup *group);
-/* Renders params->height rows split into contiguous tiles, one per device, all
- * devices given the same scene bytes, and gathers float4 rows into hostOut
- * (width*height*16 bytes).  gpuMs (may be NULL) receives the slowest device's time. */
+/* Renders the frame of params->width x params->height with pathTrace: the rows are dealt to the members in INTERLEAVED
+ * tiles of 8 rows (tile k -> member k mod n; the kernel maps a member's compact rows to global rows, so indexing is a
+ * one-GPU render's and the image is the same bit for bit), all members get the same scene bytes, each copies its tiles
+ * device to device straight into place in member 0's frame buffer on its own stream, and member 0 reads the frame back
+ * ONCE into hostOut (width*height*16 bytes).  params->row0 / rows / tileRows / tileStride are set by the library.
+ * params->accumulate != 0 continues the running sums in hostOut.  Pipelines and buffers are made on the first call and
+ * reused.  gpuMs (may be NULL) receives the slowest member's device time.  Not thread-safe per group. */
 int rtGroupRender(RTGroup *group, const char *kernelName,
                   const void *camera, const void *materials, size_t materialsLength,
                   const void *lights, size_t lightsLength,

@@ -249,25 +249,44 @@ def test_wave_kernel_odd_sample_counts_and_sizes(dev):
 
 
 def test_group_render_single_process_row_tiles(dev):
-    """rtGroupRender: one process, one host thread per device, contiguous row tiles, host gather.
-    Two group members on the same GPU exercise the split without needing a second device."""
+    """rtGroupRender: one process, interleaved 8-row tiles, every member's tiles copied device to device into place in
+    member 0's frame, one read-back.  Several group members on the same GPU exercise the deal, the strided copies and the
+    short last tile (90 rows = 11 tiles + 2 rows) without needing a second device; tools/gpu_scale.sh runs it on 2-8."""
     W, H, spp = 160, 90, 6
     osc = O.cornell(W, H)
     ref, _ = O.pathtrace(osc, W, H, spp)
     off = O.offsets(W, 0, H)
-    for ordinals in ([0], [0, 0], [0, 0, 0]):
+    for ordinals in ([0], [0, 0], [0, 0, 0], [0] * 5):
         arr = (C.c_int * len(ordinals))(*ordinals)
         g = C.c_void_p()
         L.check(L.lib.rtGroupCreate(arr, len(ordinals), C.byref(g)), "rtGroupCreate")
         assert L.lib.rtGroupDeviceCount(g) == len(ordinals)
-        p = G.default_params(W, H, spp=spp, numTriangles=36, numLights=1)
-        out = np.zeros((H, W, 4), np.float32)
         ms = C.c_double()
-        L.check(L.lib.rtGroupRender(g, b"pathTrace", O.vp(osc["camera"]), O.vp(osc["materials"]), osc["materials"].nbytes,
-                                    O.vp(osc["lights"]), osc["lights"].nbytes, O.vp(osc["vertices"]), osc["vertices"].nbytes,
-                                    None, 0, O.vp(off), C.byref(p), O.vp(out), C.byref(ms)), "rtGroupRender")
+
+        def render(sc, p, out, W=W, H=H, off=off):
+            L.check(L.lib.rtGroupRender(g, b"pathTrace", O.vp(sc["camera"]), O.vp(sc["materials"]), sc["materials"].nbytes,
+                                        O.vp(sc["lights"]), sc["lights"].nbytes, O.vp(sc["vertices"]), sc["vertices"].nbytes,
+                                        O.vp(sc["spheres"]), 0 if sc["spheres"] is None else sc["spheres"].nbytes,
+                                        O.vp(off), C.byref(p), O.vp(out), C.byref(ms)), "rtGroupRender")
+        out = np.zeros((H, W, 4), np.float32)
+        for call in range(2):                                       # the second call reuses every object of the first
+            out[:] = -1
+            render(osc, G.default_params(W, H, spp=spp, numTriangles=36, numLights=1), out)
+            assert ms.value > 0 and np.array_equal(out, ref), (ordinals, call)
+        # progressive: 2 + 4 samples accumulated through hostOut
+        acc = np.zeros((H, W, 4), np.float32)
+        render(osc, G.default_params(W, H, spp=2, firstSample=0, accumulate=1, numTriangles=36, numLights=1), acc)
+        render(osc, G.default_params(W, H, spp=4, firstSample=2, accumulate=1, numTriangles=36, numLights=1), acc)
+        assert np.all(acc[..., 3] == spp) and np.array_equal(acc[..., :3] / np.float32(spp), ref[..., :3]), ordinals
+        # another scene, another size, through the same group: spheres + four lights, 13 rows short of a tile
+        W2, H2 = 96, 77
+        ssc = O.spheres(W2, H2)
+        ref2, _ = O.pathtrace(ssc, W2, H2, 3)
+        out2 = np.zeros((H2, W2, 4), np.float32)
+        render(ssc, G.default_params(W2, H2, spp=3, numTriangles=ssc["T"], numSpheres=ssc["S"], numLights=ssc["L"]), out2,
+               W=W2, H=H2, off=O.offsets(W2, 0, H2))
+        assert np.array_equal(out2, ref2), ordinals
         L.check(L.lib.rtGroupRelease(g), "rtGroupRelease")
-        assert ms.value > 0 and np.array_equal(out, ref), ordinals
 
 
 def _set_camera(cam_bytes, pos, direction, up=(0.0, 1.0, 0.0), fov=None):

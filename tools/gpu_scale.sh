@@ -20,3 +20,10 @@ except Exception as e:
 PY
   done
 done
+# the same frames through rtGroupRender (one process, peer-to-peer gather behind the C ABI): bash tools/gpu_scale.sh ... with GROUP=1
+if [ -n "$GROUP" ]; then
+  for c in $CFGS; do for N in $NS; do
+    timeout 900 python tools/group_bench.py $N $c 3 > $O/${TAG}_group_${c}_n${N}.json 2> $O/${TAG}_group_${c}_n${N}.err
+    echo "group config $c N=$N exit $?"; cut -c1-400 $O/${TAG}_group_${c}_n${N}.json
+  done; done
+fi
