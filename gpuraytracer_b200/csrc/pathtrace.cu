@@ -638,6 +638,86 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
 }
 
 /*
+ * ALL rays of a bounce in ONE pass over the primitives: the continuation ray's closest-hit query and up to NS shadow rays
+ * (scenes with several lights), every one of them starting at the shading point.  dual_hit followed by any_hit_multi
+ * walked the scene twice and computed w, Nn (triangles) and m, C (spheres) twice; here they are computed once per
+ * primitive and bounce (256 spheres: 39 -> 32 instructions per sphere and bounce).  Same operations on the same
+ * operands in the same order per ray as tri_test / the sphere quadratic, the closest hit's candidates still met in
+ * ascending id: bit-identical results.  A shadow ray that is not wanted is given tmax = 0: nothing can be nearer.
+ */
+template <int UNROLL, int NS>
+__device__ __forceinline__ bool multi_hit(const SceneRef<false> &sc, f3 o, f3 dc, float tminC, float tmaxC, float &dist, uint32_t &id,
+                                          const f3 (&ds)[NS], const float (&tmaxS)[NS], bool (&shadowed)[NS]) {
+    float bestN = tmaxC, bestD = 1.0f;
+    uint32_t best = 0xffffffffu;
+    bool sh[NS];
+#pragma unroll
+    for (int r = 0; r < NS; r++) sh[r] = false;
+#pragma unroll 1
+    for (uint32_t i0 = 0; i0 < sc.T; i0 += UNROLL) {
+#pragma unroll
+        for (uint32_t u = 0; u < UNROLL; u++) {
+            const uint32_t i = i0 + u;
+            const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
+            const f3 n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
+            const f3 w = mk(A.x, A.y, A.z) - o;
+            const float Nn = dot(w, n);
+            float N, a;
+            {
+                const float D = dot(dc, n);
+                const f3 c = cross(dc, w);
+                if (tri_accept(D, Nn, dot(e2, c), dot(e1n, c), tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
+            }
+#pragma unroll
+            for (int r = 0; r < NS; r++) {
+                const float D = dot(ds[r], n);
+                const f3 c = cross(ds[r], w);
+                sh[r] |= tri_accept(D, Nn, dot(e2, c), dot(e1n, c), 0.0f, tmaxS[r], 1.0f, N, a);
+            }
+        }
+    }
+    if (sc.S) {
+        const float Ac = dot(dc, dc);
+        float As[NS];
+#pragma unroll
+        for (int r = 0; r < NS; r++) As[r] = dot(ds[r], ds[r]);
+#pragma unroll 1
+        for (uint32_t j0 = 0; j0 < sc.S; j0 += 2) {
+            float Bc[2], discC[2], Bs[2][NS], discS[2][NS];
+            float mx = -1.0f;
+#pragma unroll
+            for (uint32_t u = 0; u < 2; u++) {
+                const float4 R = sc.ld(sc.sph + 2 * (j0 + u));
+                const f3 m = o - mk(R.x, R.y, R.z);
+                const float Cq = fmaf(-R.w, R.w, dot(m, m));
+                Bc[u] = dot(m, dc); discC[u] = fmaf(Bc[u], Bc[u], -(Ac * Cq));
+                mx = fmaxf(mx, discC[u]);
+#pragma unroll
+                for (int r = 0; r < NS; r++) {
+                    Bs[u][r] = dot(m, ds[r]);
+                    discS[u][r] = fmaf(Bs[u][r], Bs[u][r], -(As[r] * Cq));
+                    mx = fmaxf(mx, discS[u][r]);
+                }
+            }
+            if (mx >= 0.0f) {
+#pragma unroll
+                for (uint32_t u = 0; u < 2; u++) {
+                    float N;
+                    if (sphere_roots(Bc[u], discC[u], Ac, tminC, bestN, bestD, N)) { bestN = N; bestD = Ac; best = sc.Treal + j0 + u; }
+#pragma unroll
+                    for (int r = 0; r < NS; r++) sh[r] |= sphere_roots(Bs[u][r], discS[u][r], As[r], 0.0f, tmaxS[r], 1.0f, N);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < NS; r++) shadowed[r] = sh[r];
+    id = best;
+    dist = bestN / bestD;
+    return best != 0xffffffffu;
+}
+
+/*
  * Two CAMERA rays (two samples of one pixel) in one pass: the origin is the camera for both, so the
  * four LDS.128 of a triangle record and the loop bookkeeping are shared and two independent chains
  * are in flight.  Same operations as closest_hit<PRIMARY>: bit-identical results.

@@ -318,7 +318,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                     }
                     bool hitC = false; float dist = 0.0f;
                     /* shadow rays, one per light (:79-88; the reference has one light).  The first one rides with
-                     * the continuation ray (dual_hit), the others go three / two at a time (any_hit_multi): every
+                     * the continuation ray (dual_hit; with three or four lights all of them in one multi_hit pass): every
                      * ray of a bounce starts at P, so the origin-dependent part of each test is shared. */
                     if (numLights == 1) {            /* the reference's case: its own straight-line code */
                         const float *L = sm + lay.light;
@@ -336,13 +336,17 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                         }
                         if (!shadowed) acc = acc + lightColor * color;                          /* :88 */
                     } else {
+                        /* up to four lights a pass: their shadow rays, and on the first pass the continuation ray too, share
+                         * one walk over the primitives (pathtrace.cu: multi_hit / any_hit_multi) */
                         uint32_t l = 0;
                         while (l < numLights) {
                             const uint32_t left = numLights - l;
-                            const uint32_t n = (traceC && l == 0) ? 1u : (left >= 3u ? 3u : left);
-                            f3 ldir[3], lcol[3]; float ltmax[3]; bool shd[3] = { false, false, false };
+                            const bool withC = traceC && l == 0;
+                            const uint32_t n = left >= 4u ? 4u : left;
+                            f3 ldir[4], lcol[4]; float ltmax[4]; bool shd[4] = { false, false, false, false };
 #pragma unroll
-                            for (uint32_t r = 0; r < 3; r++) {
+                            for (uint32_t r = 0; r < 4; r++) {
+                                /* (a ray that is not wanted: tmax = 0, nothing can be nearer) */
                                 ldir[r] = mk(0.0f, 1.0f, 0.0f); lcol[r] = mk(0.0f, 0.0f, 0.0f); ltmax[r] = 0.0f;
                                 if (r < n) {
                                     const float *L = sm + lay.light + RT_LIGHT_WORDS * (l + r);
@@ -353,11 +357,18 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                     ltmax[r] = ldist - 1e-3f;
                                 }
                             }
-                            if (traceC && l == 0) {
-                                hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);   /* + :49 */
-                            } else if (n == 3) {
-                                any_hit_multi<false, 2, 3>(sc, P, ldir, ltmax, shd);
-                            } else if (n == 2) {
+                            if (withC && n >= 3u) {
+                                hitC = multi_hit<2, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd);                          /* :49 + :79-88 */
+                            } else if (withC) {
+                                hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);
+                                if (n == 2u) shd[1] = any_hit<false, UNROLL>(sc, P, ldir[1], 0.0f, ltmax[1]);
+                            } else if (n == 4u) {
+                                any_hit_multi<false, 2, 4>(sc, P, ldir, ltmax, shd);
+                            } else if (n == 3u) {
+                                f3 d3[3] = { ldir[0], ldir[1], ldir[2] }; float t3[3] = { ltmax[0], ltmax[1], ltmax[2] }; bool s3[3];
+                                any_hit_multi<false, 2, 3>(sc, P, d3, t3, s3);
+                                shd[0] = s3[0]; shd[1] = s3[1]; shd[2] = s3[2];
+                            } else if (n == 2u) {
                                 f3 d2[2] = { ldir[0], ldir[1] }; float t2[2] = { ltmax[0], ltmax[1] }; bool s2[2];
                                 any_hit_multi<false, 2, 2>(sc, P, d2, t2, s2);
                                 shd[0] = s2[0]; shd[1] = s2[1];
@@ -365,7 +376,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                 shd[0] = any_hit<false, UNROLL>(sc, P, ldir[0], 0.0f, ltmax[0]);
                             }
 #pragma unroll
-                            for (uint32_t r = 0; r < 3; r++)
+                            for (uint32_t r = 0; r < 4; r++)
                                 if (r < n && !shd[r]) acc = acc + lcol[r] * color;                  /* :88, in light order */
                             l += n;
                         }
