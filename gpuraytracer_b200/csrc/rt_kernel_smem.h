@@ -35,12 +35,22 @@ RT_CX uint32_t rtWaveWords(uint32_t R, uint32_t T, uint32_t S) { return RT_BLOCK
 RT_CX uint32_t rtSortedWordsPerWarp(uint32_t R) { return (RT_SORT_FIELDS + 3u + 1u) * 32u * R + 32u + RT_SORT_KEYS; }
 RT_CX uint32_t rtSortedWords(uint32_t R, uint32_t T) { return RT_BLOCK_WARPS * rtSortedWordsPerWarp(R) + rtCullWords(T, 0u) + RT_SORT_KEYS; }
 
-/* sortedblk.cuh: 128 R slots of fields + res.xyz, two 16-bit lists and two byte arrays per slot, the lanes' offsets
- * (the wide form: every slot's Halton index), key counters (count + running), four block counters; then as above */
+/* sortedblk.cuh: 128 R slots, two 16-bit lists per slot, the lanes' offsets (the wide form: every slot's Halton index), key
+ * counters (count + running), four block counters; then as above.  A slot is
+ *   RT_SORTBLK_F4 = 0 (default)  RT_SORT_FIELDS + 3 separate words and two byte arrays (id, key): 14.5 words
+ *   RT_SORTBLK_F4 = 1            three float4 -- (X.xyz, light x) (D.xyz, light z) (colour.xyz, id | key << 8) -- + res.xyz: 15 words,
+ *                                a third of the shared-memory instructions.  MEASURED SLOWER (profiles/r04o_ab_slot_layout.log:
+ *                                16.24 against 15.94 ms at 64 spp; the wide form falls to three blocks per SM, config 5
+ *                                6 477 -> 5 582 Mpaths/s): scattered 128-bit accesses cost more wavefronts than they save
+ *                                instructions.  Kept as a switch so that it is not built a second time. */
+#ifndef RT_SORTBLK_F4
+#define RT_SORTBLK_F4 0
+#endif
 RT_CX uint32_t rtSortedBlkSlots(uint32_t R) { return RT_BLOCK_WARPS * 32u * R; }
 RT_CX uint32_t rtSortedBlkCoreWords(uint32_t R, bool wide) {
-    return (RT_SORT_FIELDS + 3u) * rtSortedBlkSlots(R) + (6u * rtSortedBlkSlots(R)) / 4u + (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) +
-           2u * RT_SORT_KEYS + 4u;
+    return (RT_SORTBLK_F4 ? 15u * rtSortedBlkSlots(R) + (4u * rtSortedBlkSlots(R)) / 4u
+                          : (RT_SORT_FIELDS + 3u) * rtSortedBlkSlots(R) + (6u * rtSortedBlkSlots(R)) / 4u) +
+           (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) + 2u * RT_SORT_KEYS + 4u;
 }
 RT_CX uint32_t rtSortedBlkWords(uint32_t R, bool wide, uint32_t T) { return rtSortedBlkCoreWords(R, wide) + rtCullWords(T, 0u) + RT_SORT_KEYS; }
 

@@ -15,6 +15,64 @@
  */
 #pragma once
 
+/* The slots of a block's round, in either layout of rt_kernel_smem.h (RT_SORTBLK_F4).  What a slot holds over a bounce:
+ * camera phase / pass B leave the hit point X and the surface id; pass A turns X into P and adds the continuation
+ * direction D, the throughput colour, x and z of the light sample point and the sort key; pass B reads all of it. */
+template <uint32_t NSLOT, bool F4>
+struct SlotStore {
+    float *Q;            /* F4: three float4 arrays A, B, C of NSLOT; else RT_SORT_FIELDS float arrays of NSLOT */
+    uint8_t *idarr, *keyarr;     /* !F4 only */
+    __device__ __forceinline__ float4 *A() const { return (float4 *)Q; }
+    __device__ __forceinline__ float4 *B() const { return (float4 *)Q + NSLOT; }
+    __device__ __forceinline__ float4 *C() const { return (float4 *)Q + 2 * NSLOT; }
+    __device__ __forceinline__ float &F(uint32_t field, uint32_t s) const { return Q[field * NSLOT + s]; }
+    /* a path that landed on a diffuse surface: hit point, colour (1,1,1), surface id */
+    __device__ __forceinline__ void put_hit_first(uint32_t s, f3 hp, uint32_t id) const {
+        if (F4) { A()[s] = make_float4(hp.x, hp.y, hp.z, 0.0f); C()[s] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(id)); }
+        else { F(0, s) = hp.x; F(1, s) = hp.y; F(2, s) = hp.z; F(6, s) = 1.0f; F(7, s) = 1.0f; F(8, s) = 1.0f; idarr[s] = (uint8_t)id; }
+    }
+    __device__ __forceinline__ void get_shade(uint32_t s, f3 &hp, f3 &color, uint32_t &id) const {
+        if (F4) { const float4 a = A()[s], c = C()[s]; hp = mk(a.x, a.y, a.z); color = mk(c.x, c.y, c.z); id = __float_as_uint(c.w) & 0xffu; }
+        else { id = idarr[s]; hp = mk(F(0, s), F(1, s), F(2, s)); color = mk(F(6, s), F(7, s), F(8, s)); }
+    }
+    __device__ __forceinline__ void put_rays(uint32_t s, f3 P, f3 rd, bool haveD, f3 color, float spx, float spz, uint32_t id, uint32_t key) const {
+        if (F4) {
+            A()[s] = make_float4(P.x, P.y, P.z, spx);
+            B()[s] = make_float4(rd.x, rd.y, rd.z, spz);
+            C()[s] = make_float4(color.x, color.y, color.z, __uint_as_float(id | (key << 8)));
+        } else {
+            F(0, s) = P.x; F(1, s) = P.y; F(2, s) = P.z;
+            if (haveD) { F(3, s) = rd.x; F(4, s) = rd.y; F(5, s) = rd.z; }
+            F(6, s) = color.x; F(7, s) = color.y; F(8, s) = color.z;
+            F(9, s) = spx; F(10, s) = spz;
+            keyarr[s] = (uint8_t)key;
+        }
+    }
+    __device__ __forceinline__ uint32_t key(uint32_t s) const {
+        return F4 ? (((const uint32_t *)C())[4u * s + 3u] >> 8) & 0xffu : (uint32_t)keyarr[s];
+    }
+    /* pass B: everything of the slot; colour and id come with the key */
+    __device__ __forceinline__ void get_trace_head(uint32_t s, f3 &color, uint32_t &surf, uint32_t &key) const {
+        if (F4) { const float4 c = C()[s]; color = mk(c.x, c.y, c.z); const uint32_t w = __float_as_uint(c.w); surf = w & 0xffu; key = (w >> 8) & 0xffu; }
+        else { key = keyarr[s]; surf = idarr[s]; color = mk(0.0f, 0.0f, 0.0f); }
+    }
+    __device__ __forceinline__ f3 get_color(uint32_t s, f3 fromHead) const { return F4 ? fromHead : mk(F(6, s), F(7, s), F(8, s)); }
+    __device__ __forceinline__ void get_trace(uint32_t s, bool haveD, f3 &P, float &spx, float &spz, f3 &rd) const {
+        if (F4) {
+            const float4 a = A()[s], b = B()[s];
+            P = mk(a.x, a.y, a.z); spx = a.w; rd = mk(b.x, b.y, b.z); spz = b.w;
+        } else {
+            P = mk(F(0, s), F(1, s), F(2, s)); spx = F(9, s); spz = F(10, s);
+            rd = haveD ? mk(F(3, s), F(4, s), F(5, s)) : mk(0.0f, 0.0f, 0.0f);
+        }
+    }
+    /* the path goes on: next hit point and surface (the key is spent) */
+    __device__ __forceinline__ void put_hit_next(uint32_t s, f3 hp, uint32_t id) const {
+        if (F4) { A()[s] = make_float4(hp.x, hp.y, hp.z, 0.0f); ((uint32_t *)C())[4u * s + 3u] = id; }
+        else { F(0, s) = hp.x; F(1, s) = hp.y; F(2, s) = hp.z; idarr[s] = (uint8_t)id; }
+    }
+};
+
 template <int R, bool SPATIAL = false>
 struct SortBlkSmem {
     static constexpr uint32_t CAP = 32u * R;                                   /* slots per warp */
@@ -27,7 +85,7 @@ struct SortBlkSmem {
      * the Halton index of every slot instead of one offset per lane */
     static constexpr uint32_t OFFS = SPATIAL ? NSLOT : RT_BLOCK_THREADS;
     static constexpr uint32_t WORDS = rtSortedBlkCoreWords(R, SPATIAL);        /* rt_kernel_smem.h: what the host launches with */
-    static_assert(WORDS == (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u + OFFS + 2u * RT_SORT_KEYS + 4u, "layout below");
+    static_assert(WORDS == (RT_SORTBLK_F4 ? 15u * NSLOT + NSLOT : (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u) + OFFS + 2u * RT_SORT_KEYS + 4u, "layout below");
 };
 
 template <int R, bool PERSIST, bool SPATIAL = false, bool MIS = false>
@@ -46,14 +104,15 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
 
+    constexpr bool F4 = RT_SORTBLK_F4 != 0;
     float *Q = sm + lay.words;
-    float *res = Q + RT_SORT_FIELDS * NSLOT;
+    float *res = Q + (F4 ? 12u : (uint32_t)RT_SORT_FIELDS) * NSLOT;
     uint16_t *hitlist = (uint16_t *)(res + 3 * NSLOT), *sorted = hitlist + NSLOT;
-    uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;
-    uint32_t *offs = (uint32_t *)(keyarr + NSLOT);
+    uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;              /* (not there with F4: id and key live in the slot) */
+    uint32_t *offs = F4 ? (uint32_t *)(sorted + NSLOT) : (uint32_t *)(keyarr + NSLOT);
+    const SlotStore<NSLOT, F4> SL = { Q, idarr, keyarr };
     uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + RT_SORT_KEYS;
     uint32_t *ctr = run + RT_SORT_KEYS;                /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
-#define SF(field, s) Q[(field) * NSLOT + (s)]
     if (threadIdx.x < 2 * RT_SORT_KEYS + 4) cnts[threadIdx.x] = 0u;
     __syncthreads();
 
@@ -202,9 +261,8 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 const uint32_t slot = warp * CAP + (s + q) * 32u + lane;
                 if (alive[q]) {
                     const uint32_t e = base + (q ? __popc(m0) : 0) + __popc((q ? m1 : m0) & lt);
-                    SF(0, slot) = hp[q].x; SF(1, slot) = hp[q].y; SF(2, slot) = hp[q].z;
-                    SF(6, slot) = 1.0f; SF(7, slot) = 1.0f; SF(8, slot) = 1.0f;
-                    hitlist[e] = (uint16_t)slot; idarr[slot] = (uint8_t)id[q];
+                    SL.put_hit_first(slot, hp[q], id[q]);
+                    hitlist[e] = (uint16_t)slot;
                 }
                 res[0 * NSLOT + slot] = r0[q].x; res[1 * NSLOT + slot] = r0[q].y; res[2 * NSLOT + slot] = r0[q].z;
             }
@@ -244,9 +302,8 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 }
                 uint32_t key = 0xffu;
                 if (active) {
-                    const uint32_t id = idarr[slot];
-                    const f3 hp = mk(SF(0, slot), SF(1, slot), SF(2, slot));
-                    f3 color = mk(SF(6, slot), SF(7, slot), SF(8, slot));
+                    uint32_t id; f3 hp, color;
+                    SL.get_shade(slot, hp, color, id);
                     const float *sh = sm + lay.shade + id;
                     const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
                     const f3 diffuse = mk(sh[(RT_SH_DR + 0) * lay.Tp], sh[(RT_SH_DR + 1) * lay.Tp], sh[(RT_SH_DR + 2) * lay.Tp]);
@@ -274,12 +331,8 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                         if (traceC) clear = clear && ray_clear_of_box(w, H, rd);
                         if (!clear) key |= 1u << g;
                     }
-                    SF(0, slot) = P.x; SF(1, slot) = P.y; SF(2, slot) = P.z;
-                    if (traceC) { SF(3, slot) = rd.x; SF(4, slot) = rd.y; SF(5, slot) = rd.z; }
-                    SF(6, slot) = color.x; SF(7, slot) = color.y; SF(8, slot) = color.z;
-                    SF(9, slot) = sp.x; SF(10, slot) = sp.z;
                     /* can the shadow ray skip the shell quads?  (rt_scene_layout.h; sorted.cuh: shadow_inside_shell) */
-                    keyarr[slot] = (uint8_t)(key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
+                    SL.put_rays(slot, P, rd, traceC, color, sp.x, sp.z, id, key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
                 }
                 if (sort) {
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
@@ -308,7 +361,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     const uint32_t e = c0 + lane;
                     const bool active = e < count;
                     const uint32_t slot = active ? hitlist[e] : 0u;
-                    const uint32_t key = active ? (keyarr[slot] & (RT_SORT_KEYS - 1u)) : 0xffu;
+                    const uint32_t key = active ? (SL.key(slot) & (RT_SORT_KEYS - 1u)) : 0xffu;
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
                     const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
                     uint32_t at = 0u;
@@ -331,7 +384,9 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 const uint32_t e = c0 + lane;
                 const bool active = e < count;
                 const uint32_t slot = active ? order[e] : 0u;
-                const uint32_t key = active ? keyarr[slot] : 0u;
+                uint32_t key = 0u, surf = 0u;
+                f3 colorHead = mk(0.0f, 0.0f, 0.0f);
+                if (active) SL.get_trace_head(slot, colorHead, surf, key);
                 __syncwarp();                                                  /* (unsorted single chunk: its entries are read before the list is rewritten) */
                 const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
                 const uint32_t pairs = keyPairs[keys & (RT_SORT_KEYS - 1u)];
@@ -340,25 +395,22 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {
-                    const f3 P = mk(SF(0, slot), SF(1, slot), SF(2, slot));
+                    f3 P, rd; float spx, spz;
+                    SL.get_trace(slot, traceC, P, spx, spz, rd);
                     const float *L = sm + lay.light;
                     f3 ldir; float ldist, inv;
-                    light_direction(mk(SF(9, slot), L[1], SF(10, slot)), P, ldir, ldist, inv);  /* sampling.metal:214-220 */
+                    light_direction(mk(spx, L[1], spz), P, ldir, ldist, inv);                   /* sampling.metal:214-220 */
                     const float ltmax = ldist - 1e-3f;                                          /* raytrace.metal:81 */
-                    const uint32_t surf = idarr[slot];
                     bool hitC = false;
                     float dist = 0.0f;
-                    f3 rd = mk(0.0f, 0.0f, 0.0f);
 #if RT_EXP_TRACE == 0
                     if (traceC) {
-                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = closest_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id);   /* :49 */
                     }
                     const bool shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);       /* :79-88 */
 #elif RT_EXP_TRACE == 1
                     bool shadowed;
                     if (traceC) {
-                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = dual_hit_pairs_masked(sc, pairs, pairsS, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
                     } else {
                         shadowed = any_hit_pairs(sc, pairsS, P, ldir, 0.0f, ltmax);
@@ -366,7 +418,6 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
 #else
                     bool shadowed;
                     if (traceC) {
-                        rd = mk(SF(3, slot), SF(4, slot), SF(5, slot));
                         hitC = dual_hit_pairs(sc, pairs, P, rd, 0.001f, 1000.0f, dist, id, ldir, 0.0f, ltmax, shadowed);
                     } else {
                         shadowed = any_hit_pairs(sc, RT_EXP_TRACE == 3 ? pairsS : pairs, P, ldir, 0.0f, ltmax);
@@ -378,7 +429,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                         f3 lightColor = light_colour(mk(L[4], L[5], L[6]), inv, ldir);
                         lightColor = lightColor * saturate(dot(normal, ldir));
                         if (MIS) lightColor = lightColor * misA_light_weight(L, P, normal, ldir);
-                        const f3 lc = lightColor * mk(SF(6, slot), SF(7, slot), SF(8, slot));
+                        const f3 lc = lightColor * SL.get_color(slot, colorHead);
                         res[0 * NSLOT + slot] = res[0 * NSLOT + slot] + lc.x;
                         res[1 * NSLOT + slot] = res[1 * NSLOT + slot] + lc.y;
                         res[2 * NSLOT + slot] = res[2 * NSLOT + slot] + lc.z;
@@ -386,7 +437,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     if (MIS) {      /* the cosine strategy's term for this continuation ray (one light on this path) */
                         const float *sh = sm + lay.shade + surf;
                         const f3 normal = mk(sh[(RT_SH_NX + 0) * lay.Tp], sh[(RT_SH_NX + 1) * lay.Tp], sh[(RT_SH_NX + 2) * lay.Tp]);
-                        const f3 term = misA_cosine_term(L, P, normal, rd, hitC, dist, mk(SF(6, slot), SF(7, slot), SF(8, slot)));
+                        const f3 term = misA_cosine_term(L, P, normal, rd, hitC, dist, SL.get_color(slot, colorHead));
                         res[0 * NSLOT + slot] = res[0 * NSLOT + slot] + term.x;
                         res[1 * NSLOT + slot] = res[1 * NSLOT + slot] + term.y;
                         res[2 * NSLOT + slot] = res[2 * NSLOT + slot] + term.z;
@@ -400,8 +451,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                             }
                         } else if (cont) {
                             alive = true;
-                            const f3 hp = P + rd * dist;
-                            SF(0, slot) = hp.x; SF(1, slot) = hp.y; SF(2, slot) = hp.z;
+                            SL.put_hit_next(slot, P + rd * dist, id);
                         }
                     }
                 }
@@ -410,7 +460,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 if (lane == 0 && mask) base = atomicAdd(&ctr[2], (uint32_t)__popc(mask));
                 base = __shfl_sync(0xffffffffu, base, 0);
                 if (alive) {
-                    hitlist[base + __popc(mask & lt)] = (uint16_t)slot; idarr[slot] = (uint8_t)id;
+                    hitlist[base + __popc(mask & lt)] = (uint16_t)slot;
                 }
             }
             __syncthreads();
@@ -459,5 +509,4 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     }
     break;
     }
-#undef SF
 }

@@ -10,5 +10,7 @@ B=../../tools/_build; mkdir -p $B
     "$@" -cubin -o $B/pt_$NAME.cubin pathtrace.cu
 /usr/local/cuda/bin/bin2c --const --name rt_cubin_image $B/pt_$NAME.cubin > $B/pt_${NAME}_cubin.c
 echo 'const unsigned long long rt_cubin_image_size = sizeof(rt_cubin_image);' >> $B/pt_${NAME}_cubin.c
-g++ -O2 -std=c++17 -fPIC -ffp-contract=off -fno-fast-math -I/usr/local/cuda/include -pthread -shared -o $B/librtcuda_$NAME.so rtcuda.cpp rt_plan.cpp host_scene.cpp host_bvh.cpp host_renderer.cpp -x c $B/pt_${NAME}_cubin.c -ldl 2>/dev/null
+# (build/noalloc.o: the runtime-API translation unit of the main build, make -C gpuraytracer_b200/csrc first)
+g++ -O2 -std=c++17 -fPIC -ffp-contract=off -fno-fast-math -I/usr/local/cuda/include -pthread -shared -o $B/librtcuda_$NAME.so rtcuda.cpp rt_plan.cpp host_scene.cpp host_bvh.cpp host_renderer.cpp build/noalloc.o -x c $B/pt_${NAME}_cubin.c \
+    -L/usr/local/cuda/lib64 -lcudart_static -Wl,--exclude-libs,libcudart_static.a -ldl -lrt -lpthread
 echo $B/librtcuda_$NAME.so
