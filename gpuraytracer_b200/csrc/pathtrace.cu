@@ -179,10 +179,15 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
                                          const unsigned char *__restrict__ spheres,
                                          float *__restrict__ scene, RTSceneLayout lay,
                                          const float4 *__restrict__ lightNormals) {
+    /* One block for the scenes the brute-force kernels take; for the BVH kernel's scenes (up to 4 M triangles) the host
+     * launches a grid: every block takes its share of the per-primitive records, block 0 alone writes the header, the
+     * lights and the object groups. */
     const int tid = threadIdx.x, nth = blockDim.x;
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gnth = gridDim.x * blockDim.x;
+    const bool lead = blockIdx.x == 0;
     const float *cam = (const float *)camera;
     const f3 position = mk(cam[0], cam[1], cam[2]);
-    if (tid == 0) {
+    if (lead && tid == 0) {
         /* generateCameraRay's per-launch part, sampling.metal:131-139 */
         const int *cami = (const int *)camera;
         f3 direction = mk(cam[4], cam[5], cam[6]);
@@ -206,7 +211,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         scene[RT_HDR_EXPOSURE] = 1.0f / (1.2f * pow_det(2.0f, ev100));   /* cameraExposure, shaders.metal:145-150 */
         for (int i = RT_HDR_EXPOSURE + 1; i < RT_HDR_WORDS; i++) if (i != RT_HDR_PAIRED) scene[i] = 0.0f;
     }
-    for (uint32_t i = tid; i < lay.Tp; i += nth) {
+    for (uint32_t i = gtid; i < lay.Tp; i += gnth) {
         float *is = scene + lay.isect + RT_ISECT_WORDS * i;
         float *ps = is + 12;
         float *sh = scene + lay.shade + i;
@@ -247,7 +252,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             for (int k = 0; k < RT_SHADE_ROWS; k++) sh[k * lay.Tp] = 0.0f;
         }
     }
-    for (uint32_t j = tid; j < lay.Sp; j += nth) {
+    for (uint32_t j = gtid; j < lay.Sp; j += gnth) {
         float *sp = scene + lay.sphere + RT_SPHERE_WORDS * j;
         float *pp = sp + 4;
         float *sh = scene + lay.sshade + j;
@@ -267,10 +272,12 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
             for (int k = 0; k < RT_SSHADE_ROWS; k++) sh[k * lay.Sp] = 0.0f;
         }
     }
+    if (!lead) return;                                    /* (block-uniform: the barriers below are block 0's own) */
     {
-        /* is every triangle 2k+1 on the v0 of triangle 2k, bit for bit?  (PAIRED loops; padding pairs are all zero) */
-        int ok = (lay.T % 2u) == 0u;
-        for (uint32_t i = 2u * tid + 1u; i < lay.T; i += 2u * nth) {
+        /* is every triangle 2k+1 on the v0 of triangle 2k, bit for bit?  (PAIRED loops; padding pairs are all zero.)
+         * Only the brute-force kernels ask: above their limit the flag stays clear and the scan is skipped. */
+        int ok = (lay.T % 2u) == 0u && lay.T <= RT_MAX_TRIANGLES;
+        for (uint32_t i = 2u * tid + 1u; i < lay.T && lay.T <= RT_MAX_TRIANGLES; i += 2u * nth) {
             const uint32_t *a = (const uint32_t *)((const SimdF3 *)vertices + 3 * (i - 1u));
             const uint32_t *b = (const uint32_t *)((const SimdF3 *)vertices + 3 * i);
             ok = ok && a[0] == b[0] && a[1] == b[1] && a[2] == b[2];
@@ -1211,6 +1218,9 @@ RT_SORTED_ENTRY(pathTrace_sorted8, 8, 3)
 RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
 
 #include "sortedblk.cuh"
+#ifndef RT_EXP_NO_FALLBACK
+#define RT_EXP_NO_FALLBACK 0     /* A/B builds only: the block-sorted entry without the compacting kernel as its fallback */
+#endif
 /* the sort taken over the block's four warps (sortedblk.cuh) */
 #define RT_SORTEDBLK_ENTRY(name, R, MINB)                                                                        \
     extern "C" __global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)                                         \
@@ -1218,9 +1228,9 @@ RT_SORTED_PERSIST_ENTRY(pathTrace_sorted_tiles6, 6, 4)
          const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters,             \
          const RTHaltonTables ht) {                                                                              \
         extern __shared__ __align__(16) float sm[];                                                              \
-        if (((const uint32_t *)scene)[lay.group + RT_GRP_OK])                                                    \
+        if (RT_EXP_NO_FALLBACK || ((const uint32_t *)scene)[lay.group + RT_GRP_OK])                             \
             pathtrace_sortedblk_body<R, false>(scene, offsets, out, p, lay, sm, RTTileSched{}, ht);              \
-        else                                                                                                     \
+        else if (!RT_EXP_NO_FALLBACK)                                                                            \
             pathtrace_wave_body<false, 4, 4, false, false>(scene, offsets, out, p, lay, sm, counters, RTTileSched{}, ht); \
     }
 RT_SORTEDBLK_ENTRY(pathTrace_sortedblk6, 6, 4)

@@ -60,3 +60,29 @@ def check_nodes(nodes, order, verts, T, max_leaf=12):
                 stack.append((r, np.maximum(lo, lo_c), np.minimum(hi, hi_c), d + 1))
     assert seen.all()
     return maxd, leaves, T / max(leaves, 1)
+
+
+def tessellate_fast(vertices, materials, T, n):
+    """tessellate() vectorised per source triangle (same points: v0 + (i/n) e1 + (j/n) e2 in fp32; the triangles come in
+    another order), for scenes of a million triangles."""
+    v = vertices.view(np.float32).reshape(T, 3, 4)
+    m = materials.reshape(T, 48)
+    inv = np.float32(1.0) / np.float32(n)
+    out_v, out_m = [], []
+    for t in range(T):
+        v0, e1, e2 = v[t, 0, :3], v[t, 1, :3] - v[t, 0, :3], v[t, 2, :3] - v[t, 0, :3]
+
+        def pt(i, j):
+            return (v0 + (i.astype(np.float32) * inv)[:, None] * e1 + (j.astype(np.float32) * inv)[:, None] * e2).astype(np.float32)
+        i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+        up = (i + j) < n                                            # (i, j), (i+1, j), (i, j+1)
+        dn = (i + j + 2) <= n                                       # (i+1, j), (i+1, j+1), (i, j+1)
+        iu, ju, idn, jdn = i[up], j[up], i[dn], j[dn]
+        tri = np.zeros((iu.size + idn.size, 3, 4), np.float32)
+        tri[:iu.size, 0, :3], tri[:iu.size, 1, :3], tri[:iu.size, 2, :3] = pt(iu, ju), pt(iu + 1, ju), pt(iu, ju + 1)
+        tri[iu.size:, 0, :3], tri[iu.size:, 1, :3], tri[iu.size:, 2, :3] = pt(idn + 1, jdn), pt(idn + 1, jdn + 1), pt(idn, jdn + 1)
+        out_v.append(tri)
+        out_m.append(np.tile(m[t], (tri.shape[0], 1)))
+    V, M = np.concatenate(out_v), np.concatenate(out_m)
+    assert V.shape[0] == T * n * n
+    return V.reshape(-1).view(np.uint8).copy(), M.reshape(-1).copy(), V.shape[0]

@@ -90,3 +90,25 @@ def test_36864_triangles_rows_against_brute_force(dev):
     for row0 in (10, 60, 100):
         ref, _ = O.pathtrace(osc, W, H, spp, row0=row0, rows=2)
         assert np.array_equal(img[row0:row0 + 2], ref), row0
+
+
+def test_a_million_triangles(dev):
+    """The advertised range (RT_MAX_TRIANGLES_BVH = 4 M): the Cornell scene cut into 36 x 167 x 167 = 1 004 004 triangles.
+    rt_prep_scene runs as a grid, the tree is built on the device, the image of sampled rows is the oracle's brute force."""
+    from bvh_util import tessellate_fast
+    W, H, spp = 64, 48, 1
+    sc, osc = G.init_cornell_box(W, H), O.cornell(W, H)
+    tv, tm, T = tessellate_fast(sc.vertices, sc.materials, 36, 167)
+    assert T == 1004004
+    sc.vertices, sc.materials, sc.num_triangles = tv, tm, T
+    osc = dict(osc, vertices=tv, materials=tm, T=T)
+    nodes, order, ms, st = device_build(dev, tv, T)
+    assert st == 0 and ms < 20.0, (ms, st)
+    print(f"device BVH build at {T} triangles: {ms:.2f} ms")
+    r = G.Renderer(sc, W, H, device=dev)
+    img = r.draw(spp=spp)
+    ms_draw = r.last_command.gpu_time_ms()
+    for row0 in (12, 30):
+        ref, _ = O.pathtrace(osc, W, H, spp, row0=row0, rows=1)
+        assert np.array_equal(img[row0:row0 + 1], ref), row0
+    print(f"  {W}x{H}x{spp} through it: {ms_draw:.2f} ms")
