@@ -127,6 +127,7 @@ extern "C" int rtPathTraceNoAlloc(const void *camera, const void *materials, con
 
     RTSceneLayout lay = rtSceneLayout(p.numTriangles, p.numSpheres, p.numLights);
     if (p.variant & RT_VARIANT_LIGHT_EXTENT) lay.flags |= RT_LAYOUT_LIGHT_EXTENT;
+    lay.flags |= RT_LAYOUT_NO_SGRID;            /* the static scratch holds the staged scene only: spheres by brute force */
     if (lay.words > RT_NOALLOC_SCENE_WORDS)     /* (cannot happen within the three limits above; the array's size is what decides) */
         return naFail(RT_ERR_OUT_OF_RANGE, "rtPathTraceNoAlloc: prepared scene of %u words exceeds the static scratch of %u", lay.words, (unsigned)RT_NOALLOC_SCENE_WORDS);
 

@@ -33,6 +33,8 @@ using namespace rt;
  * uniform datapath and cost neither LSU issue slots nor vector registers. */
 __constant__ float4 c_scene[RT_CONST_SLOTS];
 
+#include "sgrid.cuh"      /* the uniform grid over a scene's spheres: built by rt_prep_scene, walked by the intersector */
+
 /* ------------------------------------------------------------------ prep ---- */
 struct SimdF3 { float x, y, z, pad; };
 
@@ -273,6 +275,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         }
     }
     if (!lead) return;                                    /* (block-uniform: the barriers below are block 0's own) */
+    if (lay.S && !(lay.flags & RT_LAYOUT_NO_SGRID)) prep_sphere_grid(spheres, scene, lay, tid, nth);     /* sgrid.cuh */
     {
         /* is every triangle 2k+1 on the v0 of triangle 2k, bit for bit?  (PAIRED loops; padding pairs are all zero.)
          * Only the brute-force kernels ask: above their limit the flag stays clear and the scan is skipped. */
@@ -400,6 +403,7 @@ struct SceneRef {
     const float4 *base;
     uint32_t T, S;               /* PADDED loop bounds: T rounded up to 4, S to 2 */
     uint32_t Treal, sph;
+    const float *grid = nullptr;   /* the sphere grid's header in global memory (sgrid.cuh), or null: brute force over the spheres */
     __device__ __forceinline__ float4 ld(uint32_t slot) const { return CONST_BANK ? c_scene[slot] : base[slot]; }
 };
 
@@ -482,7 +486,9 @@ __device__ __forceinline__ bool any_hit(const SceneRef<CONST_BANK> &sc, f3 o, f3
             }
         }
     }
-    if (sc.S) {
+    if (sc.S && !CONST_BANK && sc.grid) {
+        if (!hit) hit = sgrid_any(sc.grid, sc.base + sc.sph, o, d, tmax);      /* (shadow rays: tmin = 0) */
+    } else if (sc.S) {
         const float A = dot(d, d);
 #pragma unroll 1
         for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
@@ -545,7 +551,10 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
             }
         }
     }
-    if (sc.S) {
+    if (sc.S && !CONST_BANK && sc.grid) {
+        sgrid_closest(sc.grid, sc.base + sc.sph, sc.Treal, o, dc, tminC, bestN, bestD, best);
+        if (!sh) sh = sgrid_any(sc.grid, sc.base + sc.sph, o, ds, tmaxS);
+    } else if (sc.S) {
         const float Ac = dot(dc, dc), As = dot(ds, ds);
 #pragma unroll 1
         for (uint32_t j0 = 0; j0 < sc.S; j0 += 4) {
@@ -609,7 +618,11 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
             }
         }
     }
-    if (sc.S) {
+    if (sc.S && !CONST_BANK && sc.grid) {
+#pragma unroll
+        for (int r = 0; r < N; r++)
+            if (!sh[r] && tmax[r] > 0.0f) sh[r] = sgrid_any(sc.grid, sc.base + sc.sph, o, d[r], tmax[r]);
+    } else if (sc.S) {
         float Aq[N];
 #pragma unroll
         for (int r = 0; r < N; r++) Aq[r] = dot(d[r], d[r]);
@@ -683,7 +696,12 @@ __device__ __forceinline__ bool multi_hit(const SceneRef<false> &sc, f3 o, f3 dc
             }
         }
     }
-    if (sc.S) {
+    if (sc.S && sc.grid) {
+        sgrid_closest(sc.grid, sc.base + sc.sph, sc.Treal, o, dc, tminC, bestN, bestD, best);
+#pragma unroll
+        for (int r = 0; r < NS; r++)
+            if (!sh[r] && tmaxS[r] > 0.0f) sh[r] = sgrid_any(sc.grid, sc.base + sc.sph, o, ds[r], tmaxS[r]);
+    } else if (sc.S) {
         const float Ac = dot(dc, dc);
         float As[NS];
 #pragma unroll

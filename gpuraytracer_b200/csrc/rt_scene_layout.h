@@ -87,6 +87,7 @@
 #define RT_LIGHT_BITANGENT 24
 #define RT_LAYOUT_LIGHT_EXTENT 1u
 #define RT_LAYOUT_LIGHT_NORMALS 2u   /* a float4-per-light normal table is bound at RT_INDEX_LIGHT_NORMALS */
+#define RT_LAYOUT_NO_SGRID 4u        /* the prepared scene has no room for the sphere grid (sgrid.cuh): brute force (rtPathTraceNoAlloc) */
 #define RT_MAX_GROUPS     4   /* cullable object groups (16 sort keys)                                 */
 #define RT_GRP_K          0
 #define RT_GRP_ALWAYS     1
@@ -110,7 +111,21 @@ typedef struct RTSceneLayout {
     uint32_t words;           /* total size                                          */
     uint32_t group;           /* object groups (sorted.cuh), RT_GROUP_WORDS words    */
     uint32_t flags;           /* RT_LAYOUT_*: how rt_prep_scene fills the sections   */
+    uint32_t sgrid;           /* sphere grid (scenes with spheres), RT_SGRID_WORDS words, in GLOBAL memory only: it starts at
+                                 `words` and is not staged into shared memory                                          */
+    uint32_t wordsGlobal;     /* size of the prepared scene in global memory: words (+ RT_SGRID_WORDS when S > 0)      */
 } RTSceneLayout;
+
+/* Sphere grid (sgrid.cuh): RT_SGRID_N^3 cells over the bounds of the spheres, each cell a list of up to RT_SGRID_CELL sphere
+ * numbers (16 bits each, 0xffff = empty) -- every sphere whose bounding cube, grown by 1/64 of a cell, overlaps the cell.
+ *   [0..2] lo.xyz of the grid   [3] ok (uint: 1 = usable; 0 = a cell overflowed or the bounds are degenerate: brute force)
+ *   [4..6] cell size xyz        [7] -
+ *   [8..10] 1 / cell size xyz   [11] -
+ *   [16 ...] RT_SGRID_N^3 cells of RT_SGRID_CELL / 2 words */
+#define RT_SGRID_N      8
+#define RT_SGRID_CELL   8
+#define RT_SGRID_HDR   16
+#define RT_SGRID_WORDS (RT_SGRID_HDR + RT_SGRID_N * RT_SGRID_N * RT_SGRID_N * (RT_SGRID_CELL / 2))
 
 #if defined(__CUDACC__)
 #define RT_HD __host__ __device__ inline
@@ -132,6 +147,8 @@ RT_HD RTSceneLayout rtSceneLayout(uint32_t T, uint32_t S, uint32_t L) {
     l.words  = l.group + RT_GROUP_WORDS;
     l.words  = (l.words + 3u) & ~3u;
     l.flags  = 0u;
+    l.sgrid  = l.words;
+    l.wordsGlobal = l.words + (S ? RT_SGRID_WORDS : 0u);
     return l;
 }
 

@@ -120,6 +120,8 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     sc.base = (const float4 *)(sm + lay.isect);
     sc.T = (lay.T + (UNROLL - 1)) / UNROLL * UNROLL; sc.S = (lay.S + 3u) & ~3u; sc.Treal = lay.T;
     sc.sph = 4 * lay.Tp;
+    /* spheres: walk the grid rt_prep_scene built (sgrid.cuh) unless it is flagged unusable */
+    if (lay.S && !(lay.flags & RT_LAYOUT_NO_SGRID) && ((const uint32_t *)scene)[lay.sgrid + 3] != 0u) sc.grid = scene + lay.sgrid;
 
     const f3 cam_o = mk(sm[RT_HDR_CAM_O], sm[RT_HDR_CAM_O + 1], sm[RT_HDR_CAM_O + 2]);
     const f3 cam_u = mk(sm[RT_HDR_CAM_U], sm[RT_HDR_CAM_U + 1], sm[RT_HDR_CAM_U + 2]);

@@ -105,6 +105,23 @@ def flops(cnt, T, S):
     return 45 * T * (Rc + Rs) + 18 * S * (Rc + Rs) + 200 * B + 60 * P
 
 
+def sgridcheck(scene, width, height, spp, *, bounces=3, seed=1, y0=0, y1=None, nthreads=0):
+    """Traces rows [y0, y1) of the frame; the sphere part of every ray query is repeated by walking the sphere grid
+    (oracle/rt_sgrid.c).  Returns dict(queries, mismatches, cells, tests, ok, first_bad[8], image)."""
+    rows = (height if y1 is None else y1) - y0
+    off = offsets(width, y0, rows, seed)
+    out = np.zeros((rows, width, 4), np.float32)
+    stats = np.zeros(5, np.uint64)
+    bad = np.zeros(8, np.float32)
+    p = RTLaunchParams(width, height, y0, rows, spp, 0, bounces, 0, scene["T"], scene["S"], scene["L"], 6, 300, 0, 0, 0)
+    rc = lib.rt_oracle_sgridcheck(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]), vp(scene["vertices"]),
+                                  vp(scene["spheres"]), vp(off), vp(out), C.byref(p), vp(stats), vp(bad), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_sgridcheck returned {rc}")
+    return dict(queries=int(stats[0]), mismatches=int(stats[1]), cells=int(stats[2]), tests=int(stats[3]), ok=bool(stats[4]),
+                first_bad=bad, image=out)
+
+
 def groups(scene):
     """The 44 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
     out = np.zeros(44, np.uint32)
