@@ -962,6 +962,17 @@ __device__ __forceinline__ f3 sample_area_light(const float *L, float ux, float 
     light_direction(light_sample_point(mk(L[0], L[1], L[2]), L[3], L[7], ux, uy), P, ldir, ldist, inv);
     return light_colour(lcolor, inv, ldir);
 }
+/* The form of the passes over several lights (wave.cuh): ONE copy of the code whichever light it is called for, with the
+ * cosine factor of raytrace.metal:75 applied.  Inlined into the unrolled four-light setup it came to 14 KB of the 42 KB the
+ * 256-sphere frame keeps executing -- against a 32 KB instruction cache, and the kernel waited for instructions 43 % of the
+ * time (profiles/r04r_c_ncu_full_summary.txt).  out: (ldir.xyz, ldist - 1e-3), (colour.xyz, -). */
+__device__ __noinline__ void sample_area_light_shaded(const float *L, float ux, float uy, f3 P, f3 normal, float4 &dirTmax, float4 &col) {
+    f3 ldir; float ldist;
+    f3 c = sample_area_light(L, ux, uy, P, ldir, ldist);
+    c = c * saturate(dot(normal, ldir));
+    dirTmax = make_float4(ldir.x, ldir.y, ldir.z, ldist - 1e-3f);
+    col = make_float4(c.x, c.y, c.z, 0.0f);
+}
 #include "mis.cuh"
 
 /* sampling.metal:39-49 */

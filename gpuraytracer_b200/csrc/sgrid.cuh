@@ -138,12 +138,24 @@ __device__ __forceinline__ uint4 sgrid_cell(const float *__restrict__ hdr, const
  * ON a cell boundary can get a first parameter a few ulps below zero (the index came from a multiplication by 1/cell, the
  * boundary from a multiplication by cell): it is clamped, -1 stays the only negative value. */
 __device__ __forceinline__ float sgrid_step(SGridWalk &w) {
-    float t;
-    if (w.tx <= w.ty && w.tx <= w.tz) { t = w.tx; w.ix += w.sx; w.tx += w.dx; if ((unsigned)w.ix >= RT_SGRID_N) return -1.0f; }
-    else if (w.ty <= w.tz)            { t = w.ty; w.iy += w.sy; w.ty += w.dy; if ((unsigned)w.iy >= RT_SGRID_N) return -1.0f; }
-    else                              { t = w.tz; w.iz += w.sz; w.tz += w.dz; if ((unsigned)w.iz >= RT_SGRID_N) return -1.0f; }
-    return t > w.tExit ? -1.0f : fmaxf(t, 0.0f);
+    /* written with selects, not branches: the lanes of a warp step along different axes */
+    const bool ax = (w.tx <= w.ty) & (w.tx <= w.tz), ay = !ax & (w.ty <= w.tz), az = !ax & !ay;
+    const float t = ax ? w.tx : ay ? w.ty : w.tz;
+    w.ix += ax ? w.sx : 0; w.iy += ay ? w.sy : 0; w.iz += az ? w.sz : 0;
+    w.tx += ax ? w.dx : 0.0f; w.ty += ay ? w.dy : 0.0f; w.tz += az ? w.dz : 0.0f;
+    /* every index is in -1 .. N: one of them outside 0 .. N-1 <=> a bit above the low three is set in their union */
+    const bool outside = (unsigned)(w.ix | w.iy | w.iz) >= (unsigned)RT_SGRID_N;
+    return (outside | (t > w.tExit)) ? -1.0f : fmaxf(t, 0.0f);
 }
+/* the cell's list as a queue: head() is its first sphere (0xffff: the list is over), pop() moves on */
+struct SGridList {
+    uint32_t a, b, c, d;
+    __device__ __forceinline__ SGridList(uint4 v) : a(v.x), b(v.y), c(v.z), d(v.w) {}
+    __device__ __forceinline__ uint32_t head() const { return a & 0xffffu; }
+    __device__ __forceinline__ void pop() {
+        a = __funnelshift_r(a, b, 16); b = __funnelshift_r(b, c, 16); c = __funnelshift_r(c, d, 16); d = (d >> 16) | 0xffff0000u;
+    }
+};
 
 /* sph: the sphere records in shared memory (float4 pairs: centre.xyz radius | prepared camera part); Treal: the number of
  * triangles (sphere j has primitive id Treal + j).  Continues the closest-hit state (bestN, bestD, best) of the triangles. */
@@ -154,13 +166,12 @@ __device__ __noinline__ void sgrid_closest(const float *__restrict__ hdr, const 
     float bestN = bestN_io, bestD = bestD_io;
     uint32_t best = best_io;
     const float A = dot(d, d), lim = tmin * A;
+#pragma unroll 1
     for (int it = 0; it < 3 * RT_SGRID_N; it++) {
-        const uint4 ids = sgrid_cell(hdr, w);
-        const uint32_t word[4] = { ids.x, ids.y, ids.z, ids.w };
-#pragma unroll
-        for (int e = 0; e < RT_SGRID_CELL; e++) {
-            const uint32_t j = (word[e >> 1] >> (16 * (e & 1))) & 0xffffu;
-            if (j == 0xffffu) break;
+        SGridList ids(sgrid_cell(hdr, w));
+#pragma unroll 1
+        for (uint32_t j = ids.head(); j != 0xffffu; j = ids.head()) {     /* (rolled: the unrolled eight were 5 KB a walk) */
+            ids.pop();
             const float4 R = sph[2 * j];
             const f3 m = o - mk(R.x, R.y, R.z);
             const float C = fmaf(-R.w, R.w, dot(m, m));
@@ -189,13 +200,12 @@ __device__ __noinline__ bool sgrid_any(const float *__restrict__ hdr, const floa
     SGridWalk w;
     if (!sgrid_begin(hdr, o, d, w)) return false;
     const float A = dot(d, d), far = tmax * A;
+#pragma unroll 1
     for (int it = 0; it < 3 * RT_SGRID_N; it++) {
-        const uint4 ids = sgrid_cell(hdr, w);
-        const uint32_t word[4] = { ids.x, ids.y, ids.z, ids.w };
-#pragma unroll
-        for (int e = 0; e < RT_SGRID_CELL; e++) {
-            const uint32_t j = (word[e >> 1] >> (16 * (e & 1))) & 0xffffu;
-            if (j == 0xffffu) break;
+        SGridList ids(sgrid_cell(hdr, w));
+#pragma unroll 1
+        for (uint32_t j = ids.head(); j != 0xffffu; j = ids.head()) {
+            ids.pop();
             const float4 R = sph[2 * j];
             const f3 m = o - mk(R.x, R.y, R.z);
             const float C = fmaf(-R.w, R.w, dot(m, m));

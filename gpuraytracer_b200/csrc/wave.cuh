@@ -86,6 +86,12 @@ __device__ __noinline__ void tiles_publish_chunk(unsigned int *flag, uint32_t ch
     if ((threadIdx.x & 31) == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(flag), "r"(chunk + 1u) : "memory");
 }
 
+/* triangles per iteration of the several-rays-a-pass loops (multi_hit, any_hit_multi): 1 -- five rays against one triangle
+ * are 2.7 KB of straight-line code already, and the 256-sphere frame is bound by instruction fetch, not by the loop's overhead */
+#ifndef RT_MULTI_UNROLL
+#define RT_MULTI_UNROLL 1
+#endif
+
 template <int R>
 struct WaveSmem {
     static constexpr uint32_t CAP = 32u * R;                                  /* paths per warp per round */
@@ -352,27 +358,26 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                 ldir[r] = mk(0.0f, 1.0f, 0.0f); lcol[r] = mk(0.0f, 0.0f, 0.0f); ltmax[r] = 0.0f;
                                 if (r < n) {
                                     const float *L = sm + lay.light + RT_LIGHT_WORDS * (l + r);
-                                    float ldist;
-                                    lcol[r] = sample_area_light(L, wx, wy, P, ldir[r], ldist);
-                                    lcol[r] = lcol[r] * saturate(dot(normal, ldir[r]));             /* :75 */
+                                    float4 dt, cl;
+                                    sample_area_light_shaded(L, wx, wy, P, normal, dt, cl);         /* :74-75 */
+                                    ldir[r] = mk(dt.x, dt.y, dt.z); ltmax[r] = dt.w; lcol[r] = mk(cl.x, cl.y, cl.z);
                                     if (MIS) lcol[r] = lcol[r] * misA_light_weight(L, P, normal, ldir[r]);
-                                    ltmax[r] = ldist - 1e-3f;
                                 }
                             }
                             if (withC && n >= 3u) {
-                                hitC = multi_hit<2, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd);                          /* :49 + :79-88 */
+                                hitC = multi_hit<RT_MULTI_UNROLL, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd);                          /* :49 + :79-88 */
                             } else if (withC) {
                                 hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);
                                 if (n == 2u) shd[1] = any_hit<false, UNROLL>(sc, P, ldir[1], 0.0f, ltmax[1]);
                             } else if (n == 4u) {
-                                any_hit_multi<false, 2, 4>(sc, P, ldir, ltmax, shd);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 4>(sc, P, ldir, ltmax, shd);
                             } else if (n == 3u) {
                                 f3 d3[3] = { ldir[0], ldir[1], ldir[2] }; float t3[3] = { ltmax[0], ltmax[1], ltmax[2] }; bool s3[3];
-                                any_hit_multi<false, 2, 3>(sc, P, d3, t3, s3);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 3>(sc, P, d3, t3, s3);
                                 shd[0] = s3[0]; shd[1] = s3[1]; shd[2] = s3[2];
                             } else if (n == 2u) {
                                 f3 d2[2] = { ldir[0], ldir[1] }; float t2[2] = { ltmax[0], ltmax[1] }; bool s2[2];
-                                any_hit_multi<false, 2, 2>(sc, P, d2, t2, s2);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 2>(sc, P, d2, t2, s2);
                                 shd[0] = s2[0]; shd[1] = s2[1];
                             } else {
                                 shd[0] = any_hit<false, UNROLL>(sc, P, ldir[0], 0.0f, ltmax[0]);
