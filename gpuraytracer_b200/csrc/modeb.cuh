@@ -138,13 +138,41 @@ __device__ __forceinline__ f3 vndf_dir(const SurfB &s, f3 viewDir, float rx, flo
 /* ------------------------------------------------------------------ kernel ---- */
 using namespace rt;
 
-/* one out-of-line copy of the closest-hit primitive loop for every secondary ray */
-__device__ __noinline__ bool closest_b(const float4 *base, uint32_t T4, uint32_t Treal, f3 o, f3 d, float tmin, float tmax,
-                                       float &dist, uint32_t &id) {
+/* One out-of-line copy of the closest-hit primitive loop for every secondary ray.
+ *
+ * On a scene rt_prep_scene could cut into object groups (sorted.cuh; the Cornell box: room, two boxes, light) a ray is
+ * tested against the always-tested quads plus those of every group whose grown box its line does not stay clear of;
+ * a ray that is a SEGMENT towards a light sample point (directSquareLightRay: tmax = the distance to `end`) and has both
+ * ends inside the shell box is not tested against the shell quads (the room's walls) either.  Mode B's rays start 1e-4 off
+ * their surface, not 1e-3 as mode A's, so the origin is asked for a quarter of the shrink only; tmin = 1e-3 does the
+ * rest (a wall's plane is crossed behind the origin or beyond the end).  The lanes of a warp walk ONE list, the union of
+ * theirs (a skip per lane gains nothing), in ascending id as the full loop: same hit, same distance bits.
+ * CPU side: oracle/rt_groups.c rt_oracle_cullcheck_modeb repeats every query of a frame under the per-ray rule
+ * (tests/test_group_cull_cpu.py).  grp: the prepared scene's group section in shared memory. */
+__device__ __noinline__ bool closest_b(const float4 *base, const float *grp, uint32_t T4, uint32_t Treal, f3 o, f3 d, float tmin,
+                                       float tmax, bool segment, f3 end, float &dist, uint32_t &id) {
     SceneRef<false> sc;
     sc.base = base; sc.S = 0; sc.Treal = Treal; sc.sph = 0;
     /* T4's top bit: the scene's triangles come in pairs on one v0 (rt_prep_scene: RT_HDR_PAIRED) */
     sc.T = T4 & 0x7fffffffu;
+    const uint32_t *gu = (const uint32_t *)grp;
+    if ((T4 & 0x80000000u) && gu[RT_GRP_OK]) {                                       /* per launch */
+        uint32_t pairs = gu[RT_GRP_ALWAYS];
+        const uint32_t K = gu[RT_GRP_K];
+        for (uint32_t g = 0; g < K; g++) {
+            const float *G = grp + 4 + 8 * g;
+            if (!ray_clear_of_box(mk(G[0], G[1], G[2]) - o, mk(G[4], G[5], G[6]), d)) pairs |= gu[4 + 8 * g + 3];
+        }
+        if (segment) {
+            const float *SB = grp + RT_GRP_SHELL_BOX;
+            const float q = 0.75f * SB[7];
+            const bool in = (fabsf(o.x - SB[0]) < SB[4] + q) & (fabsf(o.y - SB[1]) < SB[5] + q) & (fabsf(o.z - SB[2]) < SB[6] + q) &
+                            (fabsf(end.x - SB[0]) < SB[4]) & (fabsf(end.y - SB[1]) < SB[5]) & (fabsf(end.z - SB[2]) < SB[6]);
+            if (in) pairs &= ~gu[RT_GRP_SHELL];
+        }
+        pairs = __reduce_or_sync(__activemask(), pairs);
+        return closest_hit_pairs(sc, pairs, o, d, tmin, tmax, dist, id);
+    }
     if (T4 & 0x80000000u) return closest_hit<false, false, 4, true>(sc, o, d, tmin, tmax, dist, id);
     return closest_hit<false, false, 4>(sc, o, d, tmin, tmax, dist, id);
 }
@@ -178,7 +206,7 @@ __device__ __forceinline__ f3 direct_light(const float *sm, const RTSceneLayout 
     f3 ldir = toLight / distance;
     float dist; uint32_t id;
     rays++;
-    if (!closest_b(base, T4, lay.T, origin, ldir, 0.001f, distance, dist, id)) return mk(0.0f, 0.0f, 0.0f);
+    if (!closest_b(base, sm + lay.group, T4, lay.T, origin, ldir, 0.001f, distance, true, samplePos, dist, id)) return mk(0.0f, 0.0f, 0.0f);
     if (sm[lay.shade + id + RT_SH_FLAG * lay.Tp] == 0.0f) return mk(0.0f, 0.0f, 0.0f);       /* not HitLight */
     f3 brdf = brdf_contribution(s, ldir);
     float directLightPDF = square_light_pdf(s.point, L, ldir);
@@ -294,7 +322,7 @@ drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, f
                                 : power_heuristic(cosinePDF, directLightPDF, vndfPDF, nf);
             float d2; uint32_t id2;
             rays++;
-            bool hit2 = closest_b(base, T4, lay.T, origin, dir, 0.001f, 1000.0f, d2, id2);
+            bool hit2 = closest_b(base, sm + lay.group, T4, lay.T, origin, dir, 0.001f, 1000.0f, false, origin, d2, id2);
             f3 brdf = brdf_contribution(in, dir);
             f3 add = mk(0.0f, 0.0f, 0.0f);
             bool contributes = false;

@@ -169,7 +169,7 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
             r[k] = shell ? (alo[k] + ahi[k]) * 0.5f : 0.0f;
             r[4 + k] = shell ? (ahi[k] - alo[k]) * 0.5f - shrink : 0.0f;
         }
-        r[3] = 0.0f; r[7] = 0.0f;
+        r[3] = 0.0f; r[7] = shell ? shrink : 0.0f;                         /* (modeb.cuh asks the origin for a quarter of it) */
         gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; gu[RT_GRP_SHELL] = shell;
     }
 }

@@ -30,7 +30,7 @@
  *            its vertices grown by 1/128 of the scene's largest extent.
  *            [3] the SHELL: those always-tested quads that lie in a face plane of the always-tested quads' own bounds
  *            (all six vertices bit-equal to the bound on one axis: the walls of a room).  After the K records, 8 words:
- *            centre xyz of those bounds, - | half extent xyz shrunk by 1/16384 of the scene's largest extent, -.
+ *            centre xyz of those bounds, - | half extent xyz shrunk by 1/16384 of the scene's largest extent, that shrink.
  *            A shadow ray whose two ends both lie inside the shrunk box cannot be accepted by a shell quad (the
  *            segment stays 3e-4 x extent clear of its plane; the test's own error is 1e-6 x extent), so those
  *            any-hit tests are skipped (sortedblk.cuh / sorted.cuh, pass B).

@@ -107,6 +107,7 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
         float *r = (float *)out + RT_GRP_SHELL_BOX;
         const float shrink = ext * (1.0f / 16384.0f);
         for (int k = 0; k < 3; k++) { r[k] = (alo[k] + ahi[k]) * 0.5f; r[4 + k] = (ahi[k] - alo[k]) * 0.5f - shrink; }
+        r[7] = shrink;
     }
     out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u; out[3] = shell;
     return (int)K;
@@ -208,5 +209,64 @@ int rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials, 
     rt_oracle_query_hook = 0;
     stats[0] = g_chk.queries; stats[1] = g_chk.mismatches; stats[2] = g_chk.culledTests; stats[3] = g_chk.fullTests;
     for (int k = 0; k < 16; k++) { stats[4 + k] = g_chk.keysDual[k]; stats[20 + k] = g_chk.keysSingle[k]; }
+    return rc;
+}
+
+/* ---- mode B (csrc/modeb.cuh: closest_b): the same box rule per ray, and the shell rule for the rays that are segments towards
+ * a light sample point.  Mode B's rays start 1e-4 off their surface (shaders.metal:527), not 1e-3, so the origin is asked
+ * to lie inside the box shrunk by a QUARTER of the shrink only (1/65536 of the extent; the end as in mode A), and the
+ * ray's tmin = 1e-3 does the rest: a shell quad's plane is crossed behind the origin or beyond the end.
+ * Per ray here; the kernel tests the union of a warp's lists, a superset in the same ascending order. */
+extern void (*rt_oracle_modeb_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int seg, const float end[3],
+                                          int hit, float distance, uint32_t primitive_id);
+static struct { uint64_t queries, mismatches, culledTests, fullTests, segQueries, segInShell; } g_b;
+
+static void cull_hook_b(const float o[3], const float d[3], float tmin, float tmax, int seg, const float end[3],
+                        int hit, float distance, uint32_t primitive_id) {
+    const uint32_t K = g_chk.words[0];
+    uint32_t pairs = g_chk.words[1];
+    for (uint32_t g = 0; g < K; g++) {
+        const float *r = (const float *)g_chk.words + 4 + 8 * g;
+        const float w[3] = { r[0] - o[0], r[1] - o[1], r[2] - o[2] };
+        if (!ray_clear_of_box(w, r + 4, d)) pairs |= g_chk.words[4 + 8 * g + 3];
+    }
+    int in = 0;
+    if (seg) {
+        const float *bx = (const float *)g_chk.words + RT_GRP_SHELL_BOX;
+        in = 1;
+        for (int k = 0; k < 3; k++)
+            in = in && fabsf(o[k] - bx[k]) < bx[4 + k] + 0.75f * bx[7] && fabsf(end[k] - bx[k]) < bx[4 + k];
+        if (in) pairs &= ~g_chk.words[3];
+    }
+    int h = 0; uint32_t id = 0, tests = 0;
+    float bestN = tmax, bestD = 1.0f;
+    for (uint32_t i = 0; i < g_chk.T; i++) {
+        if (!((pairs >> (i / 2)) & 1u)) continue;
+        const float *v = g_chk.vertices + (size_t)i * 12;
+        tests++;
+        if (rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &bestN, &bestD)) { h = 1; id = i; }
+    }
+    const float dist = h ? bestN / bestD : 0.0f;
+    const int bad = h != hit || (h && (id != primitive_id || memcmp(&dist, &distance, 4)));
+#pragma omp critical
+    {
+        g_b.queries++; g_b.mismatches += bad; g_b.culledTests += tests; g_b.fullTests += g_chk.T;
+        g_b.segQueries += seg != 0; g_b.segInShell += in;
+    }
+}
+
+/* stats: queries, mismatches, triangle tests with culling, without, segment queries, of those inside the shell box */
+int rt_oracle_cullcheck_modeb(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                              const simd_float3 *vertices, uint8_t *pixels, float *text,
+                              const RTLaunchParams *params, uint64_t stats[6], int nthreads) {
+    memset(&g_chk, 0, sizeof g_chk); memset(&g_b, 0, sizeof g_b);
+    rt_oracle_groups(vertices, params->numTriangles, lights, params->numLights, g_chk.words);
+    g_chk.vertices = (const float *)vertices; g_chk.T = params->numTriangles;
+    rt_oracle_modeb_query_hook = cull_hook_b;
+    uint64_t cnt[RT_CNT_COUNT];
+    int rc = rt_oracle_drawtriangle(cameras, materials, lights, vertices, pixels, text, params, cnt, nthreads);
+    rt_oracle_modeb_query_hook = 0;
+    stats[0] = g_b.queries; stats[1] = g_b.mismatches; stats[2] = g_b.culledTests; stats[3] = g_b.fullTests;
+    stats[4] = g_b.segQueries; stats[5] = g_b.segInShell;
     return rc;
 }

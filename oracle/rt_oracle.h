@@ -107,6 +107,18 @@ int  rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials,
                          const simd_float3 *vertices, const uint32_t *offsets, float *out,
                          const RTLaunchParams *params, uint64_t stats[36], int nthreads);
 
+/* mode B's form of the same check (every closest-hit query of a drawTriangle frame; the shell rule for the rays that are
+ * segments towards a light sample point): stats = queries, mismatches (must be 0), triangle tests with / without culling,
+ * segment queries, of those with both ends inside the shell box */
+int  rt_oracle_cullcheck_modeb(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                               const simd_float3 *vertices, uint8_t *pixels, float *text,
+                               const RTLaunchParams *params, uint64_t stats[6], int nthreads);
+/* the sphere grid's check (rt_sgrid.c): stats = queries, mismatches (must be 0), cells visited, sphere tests made, grid
+ * usable; firstBad = the first failing query (o, d, tmax, any) */
+int  rt_oracle_sgridcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                          const simd_float3 *vertices, const SphereGPU *spheres, const uint32_t *offsets, float *out,
+                          const RTLaunchParams *params, uint64_t stats[5], float firstBad[8], int nthreads);
+
 int  rt_oracle_max_threads(void);
 
 #ifdef __cplusplus

@@ -203,6 +203,13 @@ static inline v3 calculateBRDFContribution(v3 rayDirection, v3 normal, const ise
     return scale(BRDF, NoL);
 }
 
+/* test hook (rt_groups.c: rt_oracle_cullcheck_modeb): every closest-hit query of the frame with its answer; seg = the ray is
+ * a segment towards a light sample point (directSquareLightRay), whose end is then in rt_oracle_modeb_segment_end */
+void (*rt_oracle_modeb_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int seg, const float end[3],
+                                   int hit, float distance, uint32_t primitive_id);
+static _Thread_local float t_segment_end[3];
+static _Thread_local int t_segment;
+
 /* :291-313 */
 static inline ray_t directSquareLightRay(v3 origin, const SquareLightGPU *light, float rx, float ry) {
     v3 lightNormal = mk(0, -1, 0);
@@ -219,6 +226,7 @@ static inline ray_t directSquareLightRay(v3 origin, const SquareLightGPU *light,
     r.direction = lightDir;
     r.min_distance = 0.001f;
     r.max_distance = distance;
+    t_segment_end[0] = samplePos.x; t_segment_end[1] = samplePos.y; t_segment_end[2] = samplePos.z; t_segment = 1;
     return r;
 }
 
@@ -305,6 +313,9 @@ static inline isect_t getClosestIntersection(const ctx_t *c, ray_t in) {
     float o[3] = { in.origin.x, in.origin.y, in.origin.z }, d[3] = { in.direction.x, in.direction.y, in.direction.z };
     c->cnt[RT_CNT_CLOSEST_RAYS]++;
     rt_hit h = rt_intersect((const float *)c->vertices, c->T, NULL, 0, o, d, in.min_distance, in.max_distance, 0);
+    if (rt_oracle_modeb_query_hook)
+        rt_oracle_modeb_query_hook(o, d, in.min_distance, in.max_distance, t_segment, t_segment_end, h.hit, h.distance, h.primitive_id);
+    t_segment = 0;
     isect_t r;
     memset(&r, 0, sizeof r);
     if (!h.hit) { r.type = MISS; return r; }

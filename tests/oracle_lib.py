@@ -105,6 +105,21 @@ def flops(cnt, T, S):
     return 45 * T * (Rc + Rs) + 18 * S * (Rc + Rs) + 200 * B + 60 * P
 
 
+def cullcheck_modeb(scene, width, height, *, camera_rays=6, mis_samples=300, nthreads=0):
+    """Traces a drawTriangle frame; every closest-hit query is repeated against the quads the group / shell rule leaves.
+    Returns dict(queries, mismatches, culled_tests, full_tests, seg_queries, seg_in_shell, text)."""
+    pixels = np.zeros((height, width, 4), np.uint8)
+    text = np.zeros((height, width, 3), np.float32)
+    stats = np.zeros(6, np.uint64)
+    p = RTLaunchParams(width, height, 0, height, 0, 0, 0, 0, scene["T"], 0, scene["L"], camera_rays, mis_samples, 0, 0, 0)
+    rc = lib.rt_oracle_cullcheck_modeb(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]), vp(scene["vertices"]),
+                                       vp(pixels), vp(text), C.byref(p), vp(stats), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_cullcheck_modeb returned {rc}")
+    return dict(queries=int(stats[0]), mismatches=int(stats[1]), culled_tests=int(stats[2]), full_tests=int(stats[3]),
+                seg_queries=int(stats[4]), seg_in_shell=int(stats[5]), text=text, pixels=pixels)
+
+
 def sgridcheck(scene, width, height, spp, *, bounces=3, seed=1, y0=0, y1=None, nthreads=0):
     """Traces rows [y0, y1) of the frame; the sphere part of every ray query is repeated by walking the sphere grid
     (oracle/rt_sgrid.c).  Returns dict(queries, mismatches, cells, tests, ok, first_bad[8], image)."""

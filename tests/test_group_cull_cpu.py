@@ -105,3 +105,16 @@ def test_culling_never_changes_a_query_random_boxes():
         assert r["mismatches"] == 0, (scene, r["mismatches"])
         total += r["queries"]
     assert total > 2_500_000
+
+
+def test_culling_never_changes_a_query_modeb_frame():
+    """Mode B (csrc/modeb.cuh: closest_b): the box rule per ray and the shell rule for the segments towards a light sample
+    point, whose origins sit 1e-4 off their surface (mode A: 1e-3) -- every closest-hit query of a drawTriangle frame."""
+    for W, H, ls in ((96, 64, 1.5), (64, 48, 1.0)):
+        sc = O.cornell(W, H, light_size=ls)
+        r = O.cullcheck_modeb(sc, W, H, camera_rays=2, mis_samples=60)
+        _, ref, _ = O.drawtriangle(sc, W, H, camera_rays=2, mis_samples=60)
+        assert np.array_equal(r["text"], ref)              # the hook does not disturb the oracle
+        assert r["queries"] > 400_000 and r["mismatches"] == 0
+        assert r["culled_tests"] < 0.3 * r["full_tests"]
+        assert r["seg_in_shell"] > 0.999 * r["seg_queries"] > 0
