@@ -59,8 +59,18 @@ __device__ __forceinline__ float power_heuristic(float pdf1, float pdf2, float p
     return p1 / (sum + 1e-6f);
 }
 
-/* :259-289 */
-__device__ __forceinline__ f3 brdf_contribution(const SurfB &s, f3 l) {
+/* :259-289.  ONE copy for its three callers (RT_MODEB_OUTLINE): with the primitive loop cut down by the group rule the
+ * kernel's time went to fetching the shading code, 32 KB of it executed against a 32 KB instruction cache
+ * (profiles/r04t_modeb_ncu_full_summary.txt: 22 % of the stall samples "no instruction") */
+#ifndef RT_MODEB_OUTLINE
+#define RT_MODEB_OUTLINE 1
+#endif
+#if RT_MODEB_OUTLINE
+#define RT_MODEB_FN __noinline__
+#else
+#define RT_MODEB_FN __forceinline__
+#endif
+__device__ RT_MODEB_FN f3 brdf_contribution(const SurfB &s, f3 l) {
     f3 v = -normalize(s.rdir);
     f3 n = s.normal;
     f3 h = normalize(v + l);
@@ -194,7 +204,7 @@ __device__ __forceinline__ bool load_surface(const float *sm, const RTSceneLayou
 }
 
 /* calculateDirectLightSamplingContribution, :519-541 (directSquareLightRay :291-313 inlined) */
-__device__ __forceinline__ f3 direct_light(const float *sm, const RTSceneLayout &lay, const float4 *base, uint32_t T4,
+__device__ RT_MODEB_FN f3 direct_light(const float *sm, const RTSceneLayout &lay, const float4 *base, uint32_t T4,
                                            const LightB &L, const SurfB &s, float rx, float ry, float n, bool usePower,
                                            uint32_t &rays) {
     f3 origin = s.point + s.normal * 1e-4f;
@@ -220,8 +230,11 @@ __device__ __forceinline__ f3 direct_light(const float *sm, const RTSceneLayout 
 }
 
 #define RT_MODEB_THREADS 128
+#ifndef RT_MODEB_MINBLOCKS
+#define RT_MODEB_MINBLOCKS 4      /* 128 registers, no spills: 45.3 M camera rays/s; 3 (149 registers): 42.7; 5 (96): 44.5 */
+#endif
 
-extern "C" __global__ void __launch_bounds__(RT_MODEB_THREADS, 3)
+extern "C" __global__ void __launch_bounds__(RT_MODEB_THREADS, RT_MODEB_MINBLOCKS)
 drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, float *__restrict__ text,
                  const RTLaunchParams p, const RTSceneLayout lay, unsigned long long *__restrict__ counters) {
     extern __shared__ __align__(16) float sm[];

@@ -166,9 +166,13 @@ __device__ __noinline__ void sgrid_closest(const float *__restrict__ hdr, const 
     float bestN = bestN_io, bestD = bestD_io;
     uint32_t best = best_io;
     const float A = dot(d, d), lim = tmin * A;
+    /* the NEXT cell's list is asked for before this cell's spheres are tested, so that its way from the cache overlaps them */
+    SGridList ids(sgrid_cell(hdr, w));
 #pragma unroll 1
     for (int it = 0; it < 3 * RT_SGRID_N; it++) {
-        SGridList ids(sgrid_cell(hdr, w));
+        const float t = sgrid_step(w);
+        uint4 nxt = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+        if (t >= 0.0f) nxt = sgrid_cell(hdr, w);
 #pragma unroll 1
         for (uint32_t j = ids.head(); j != 0xffffu; j = ids.head()) {     /* (rolled: the unrolled eight were 5 KB a walk) */
             ids.pop();
@@ -188,9 +192,9 @@ __device__ __noinline__ void sgrid_closest(const float *__restrict__ hdr, const 
                 }
             }
         }
-        const float t = sgrid_step(w);
         if (t < 0.0f) break;
         if (t * bestD > bestN * 1.0001f) break;                          /* the rest of the walk lies behind the best hit */
+        ids = SGridList(nxt);
     }
     bestN_io = bestN; bestD_io = bestD; best_io = best;
 }
@@ -200,9 +204,13 @@ __device__ __noinline__ bool sgrid_any(const float *__restrict__ hdr, const floa
     SGridWalk w;
     if (!sgrid_begin(hdr, o, d, w)) return false;
     const float A = dot(d, d), far = tmax * A;
+    SGridList ids(sgrid_cell(hdr, w));
 #pragma unroll 1
     for (int it = 0; it < 3 * RT_SGRID_N; it++) {
-        SGridList ids(sgrid_cell(hdr, w));
+        const float t = sgrid_step(w);
+        const bool more = (t >= 0.0f) & (t <= tmax);
+        uint4 nxt = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+        if (more) nxt = sgrid_cell(hdr, w);
 #pragma unroll 1
         for (uint32_t j = ids.head(); j != 0xffffu; j = ids.head()) {
             ids.pop();
@@ -218,8 +226,8 @@ __device__ __noinline__ bool sgrid_any(const float *__restrict__ hdr, const floa
                 if (((N0 >= 0.0f * A) & (N0 * 1.0f < far)) | ((N1 >= 0.0f * A) & (N1 * 1.0f < far))) return true;
             }
         }
-        const float t = sgrid_step(w);
-        if (t < 0.0f || t > tmax) break;
+        if (!more) break;
+        ids = SGridList(nxt);
     }
     return false;
 }
