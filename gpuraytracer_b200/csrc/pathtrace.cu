@@ -161,6 +161,13 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
         face = face || (mine && lo[k] == hi[k] && (lo[k] == alo[k] || lo[k] == ahi[k]));
     }
     const uint32_t shell = __ballot_sync(0xffffffffu, face);
+    /* the shell quads face by face (the exit rule, rt_scene_layout.h) */
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const uint32_t loFace = __ballot_sync(0xffffffffu, face && lo[k] == hi[k] && lo[k] == alo[k]);
+        const uint32_t hiFace = __ballot_sync(0xffffffffu, face && lo[k] == hi[k] && lo[k] == ahi[k]);
+        if (lane == 0) { gu[RT_GRP_FACES + 2 * k] = loFace; gu[RT_GRP_FACES + 2 * k + 1] = hiFace; }
+    }
     if (lane == 0) {
         float *r = gf + RT_GRP_SHELL_BOX;
         const float shrink = ext * (1.0f / 16384.0f);
@@ -169,7 +176,7 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
             r[k] = shell ? (alo[k] + ahi[k]) * 0.5f : 0.0f;
             r[4 + k] = shell ? (ahi[k] - alo[k]) * 0.5f - shrink : 0.0f;
         }
-        r[3] = 0.0f; r[7] = shell ? shrink : 0.0f;                         /* (modeb.cuh asks the origin for a quarter of it) */
+        r[3] = shell ? margin : 0.0f; r[7] = shell ? shrink : 0.0f;      /* (modeb.cuh asks the origin for a quarter of the shrink) */
         gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; gu[RT_GRP_SHELL] = shell;
     }
 }

@@ -15,6 +15,7 @@
 #define RT_WAVE_RES      3      /* result slots per path                                                              */
 #define RT_SORT_FIELDS  11      /* sorted.cuh slot: X.xyz (hit point, then P)  D.xyz  colour.xyz  light sample x, z   */
 #define RT_SORT_KEYS    (1 << RT_MAX_GROUPS)
+#define RT_SORTBLK_KEYS (8 << RT_MAX_GROUPS)   /* sortedblk.cuh: the groups' bits above three bits of exit face (rt_scene_layout.h) */
 
 #if defined(__CUDACC__)
 #define RT_CX __host__ __device__ constexpr
@@ -36,7 +37,7 @@ RT_CX uint32_t rtSortedWordsPerWarp(uint32_t R) { return (RT_SORT_FIELDS + 3u + 
 RT_CX uint32_t rtSortedWords(uint32_t R, uint32_t T) { return RT_BLOCK_WARPS * rtSortedWordsPerWarp(R) + rtCullWords(T, 0u) + RT_SORT_KEYS; }
 
 /* sortedblk.cuh: 128 R slots, two 16-bit lists per slot, the lanes' offsets (the wide form: every slot's Halton index), key
- * counters (count + running), four block counters; then as above.  A slot is
+ * counters (count, running, start), four block counters; then as above.  A slot is
  *   RT_SORTBLK_F4 = 0 (default)  RT_SORT_FIELDS + 3 separate words and two byte arrays (id, key): 14.5 words
  *   RT_SORTBLK_F4 = 1            three float4 -- (X.xyz, light x) (D.xyz, light z) (colour.xyz, id | key << 8) -- + res.xyz: 15 words,
  *                                a third of the shared-memory instructions.  MEASURED SLOWER (profiles/r04o_ab_slot_layout.log:
@@ -50,8 +51,9 @@ RT_CX uint32_t rtSortedBlkSlots(uint32_t R) { return RT_BLOCK_WARPS * 32u * R; }
 RT_CX uint32_t rtSortedBlkCoreWords(uint32_t R, bool wide) {
     return (RT_SORTBLK_F4 ? 15u * rtSortedBlkSlots(R) + (4u * rtSortedBlkSlots(R)) / 4u
                           : (RT_SORT_FIELDS + 3u) * rtSortedBlkSlots(R) + (6u * rtSortedBlkSlots(R)) / 4u) +
-           (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) + 2u * RT_SORT_KEYS + 4u;
+           (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) + 3u * RT_SORTBLK_KEYS + 4u;
 }
-RT_CX uint32_t rtSortedBlkWords(uint32_t R, bool wide, uint32_t T) { return rtSortedBlkCoreWords(R, wide) + rtCullWords(T, 0u) + RT_SORT_KEYS; }
+/* (after the core: candidate bits, unit word, the key -> quads tables of the continuation ray and of the shadow ray) */
+RT_CX uint32_t rtSortedBlkWords(uint32_t R, bool wide, uint32_t T) { return rtSortedBlkCoreWords(R, wide) + rtCullWords(T, 0u) + RT_SORTBLK_KEYS + RT_SORT_KEYS; }
 
 #endif

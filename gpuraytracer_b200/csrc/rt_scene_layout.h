@@ -30,7 +30,12 @@
  *            its vertices grown by 1/128 of the scene's largest extent.
  *            [3] the SHELL: those always-tested quads that lie in a face plane of the always-tested quads' own bounds
  *            (all six vertices bit-equal to the bound on one axis: the walls of a room).  After the K records, 8 words:
- *            centre xyz of those bounds, - | half extent xyz shrunk by 1/16384 of the scene's largest extent, that shrink.
+ *            centre xyz of those bounds, the groups' margin (1/128 of the extent) | half extent xyz shrunk by 1/16384 of the
+ *            scene's largest extent, that shrink.  Then the shell quads face by face (RT_GRP_FACES), for the EXIT RULE: a
+ *            closest-hit ray that starts inside the shrunk box can be accepted by a shell quad only where it crosses that
+ *            quad's face plane ahead of it, and only if the crossing point lies within the face grown by the margin; so
+ *            the ray is tested against the shell quads of the faces it can leave the box through -- one, as a rule --
+ *            instead of all of them (sortedblk.cuh: part of the sort key).
  *            A shadow ray whose two ends both lie inside the shrunk box cannot be accepted by a shell quad (the
  *            segment stays 3e-4 x extent clear of its plane; the test's own error is 1e-6 x extent), so those
  *            any-hit tests are skipped (sortedblk.cuh / sorted.cuh, pass B).
@@ -94,7 +99,8 @@
 #define RT_GRP_OK         2
 #define RT_GRP_SHELL      3
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
-#define RT_GROUP_WORDS   (RT_GRP_SHELL_BOX + 8)
+#define RT_GRP_FACES     (RT_GRP_SHELL_BOX + 8)     /* 6 pair masks: the shell quads in face 2 * axis + (1 = high side); 2 spare words */
+#define RT_GROUP_WORDS   (RT_GRP_FACES + 8)
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */
 #define RT_CONST_SLOTS   3584

@@ -190,6 +190,34 @@ __device__ __forceinline__ bool shadow_inside_shell(const float *SB, f3 P, f3 sp
     return (fabsf(P.x - SB[0]) < SB[4]) & (fabsf(P.y - SB[1]) < SB[5]) & (fabsf(P.z - SB[2]) < SB[6]) &
            (fabsf(sp.x - SB[0]) < SB[4]) & (fabsf(sp.y - SB[1]) < SB[5]) & (fabsf(sp.z - SB[2]) < SB[6]);
 }
+/* The exit rule (rt_scene_layout.h): through which face of the shell box can the closest-hit ray from P along d leave it?
+ * 0..5 = face 2 * axis + (1 = high side): only that face's shell quads can accept the ray; 6 = none can (it leaves through a
+ * face without quads, or runs in a face's plane); 7 = test them all (P is not inside the shrunk box, or the crossing points
+ * of two faces lie within the margin of the box: an edge).  The crossing point comes from an approximate reciprocal -- it
+ * is compared with a face grown by 1/128 of the scene, four orders above the exact test's own reach; a NaN keeps the face.
+ * CPU side: oracle/rt_groups.c exit_rule, over every query of a frame. */
+__device__ __forceinline__ uint32_t exit_face_code(const float *SB, f3 P, f3 d) {
+    const bool inside = (fabsf(P.x - SB[0]) < SB[4]) & (fabsf(P.y - SB[1]) < SB[5]) & (fabsf(P.z - SB[2]) < SB[6]);
+    const float s = SB[7], m = s + SB[3];
+    const float hx = SB[4] + s, hy = SB[5] + s, hz = SB[6] + s;
+    uint32_t n = 0u, code = 6u;
+    {
+        const float t = __fdividef((d.x > 0.0f ? SB[0] + hx : SB[0] - hx) - P.x, d.x);
+        const float py = fmaf(t, d.y, P.y), pz = fmaf(t, d.z, P.z);
+        if ((d.x != 0.0f) & !(fabsf(py - SB[1]) > SB[5] + m) & !(fabsf(pz - SB[2]) > SB[6] + m)) { n++; code = d.x > 0.0f ? 1u : 0u; }
+    }
+    {
+        const float t = __fdividef((d.y > 0.0f ? SB[1] + hy : SB[1] - hy) - P.y, d.y);
+        const float px = fmaf(t, d.x, P.x), pz = fmaf(t, d.z, P.z);
+        if ((d.y != 0.0f) & !(fabsf(px - SB[0]) > SB[4] + m) & !(fabsf(pz - SB[2]) > SB[6] + m)) { n++; code = d.y > 0.0f ? 3u : 2u; }
+    }
+    {
+        const float t = __fdividef((d.z > 0.0f ? SB[2] + hz : SB[2] - hz) - P.z, d.z);
+        const float px = fmaf(t, d.x, P.x), py = fmaf(t, d.y, P.y);
+        if ((d.z != 0.0f) & !(fabsf(px - SB[0]) > SB[4] + m) & !(fabsf(py - SB[1]) > SB[5] + m)) { n++; code = d.z > 0.0f ? 5u : 4u; }
+    }
+    return (!inside | (n > 1u)) ? 7u : code;
+}
 #define RT_KEY_SHELL 0x80u     /* bit of keyarr[]: the shadow ray must be tested against the shell quads too */
 
 __device__ __forceinline__ bool any_hit_pairs(const SceneRef<false> &sc, uint32_t pairs, f3 o, f3 d, float tmin, float tmax) {

@@ -85,7 +85,7 @@ struct SortBlkSmem {
      * the Halton index of every slot instead of one offset per lane */
     static constexpr uint32_t OFFS = SPATIAL ? NSLOT : RT_BLOCK_THREADS;
     static constexpr uint32_t WORDS = rtSortedBlkCoreWords(R, SPATIAL);        /* rt_kernel_smem.h: what the host launches with */
-    static_assert(WORDS == (RT_SORTBLK_F4 ? 15u * NSLOT + NSLOT : (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u) + OFFS + 2u * RT_SORT_KEYS + 4u, "layout below");
+    static_assert(WORDS == (RT_SORTBLK_F4 ? 15u * NSLOT + NSLOT : (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u) + OFFS + 3u * RT_SORTBLK_KEYS + 4u, "layout below");
 };
 
 template <int R, bool PERSIST, bool SPATIAL = false, bool MIS = false>
@@ -111,9 +111,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;              /* (not there with F4: id and key live in the slot) */
     uint32_t *offs = F4 ? (uint32_t *)(sorted + NSLOT) : (uint32_t *)(keyarr + NSLOT);
     const SlotStore<NSLOT, F4> SL = { Q, idarr, keyarr };
-    uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + RT_SORT_KEYS;
-    uint32_t *ctr = run + RT_SORT_KEYS;                /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
-    if (threadIdx.x < 2 * RT_SORT_KEYS + 4) cnts[threadIdx.x] = 0u;
+    constexpr uint32_t NK = RT_SORTBLK_KEYS;           /* sort keys: exit face (3 bits) under the groups' bits; bit 7 of a key byte is RT_KEY_SHELL */
+    uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + NK, *startOf = run + NK;
+    uint32_t *ctr = startOf + NK;                      /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
+    for (uint32_t k = threadIdx.x; k < 3 * NK + 4; k += RT_BLOCK_THREADS) cnts[k] = 0u;
     __syncthreads();
 
     SceneRef<false> sc;
@@ -133,12 +134,16 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     const float *shellBox = sm + lay.group + RT_GRP_SHELL_BOX;
     const uint32_t mwT = (lay.T + 31u) >> 5;
     uint32_t *tail = (uint32_t *)(sm + lay.words + SortBlkSmem<R, SPATIAL>::WORDS);
-    /* the quads each key names: always-tested ones + those of the groups whose bit is set */
-    uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1;
-    if (threadIdx.x < RT_SORT_KEYS) {
-        uint32_t pm = grp[RT_GRP_ALWAYS];
-        for (uint32_t g = 0; g < K; g++) if ((threadIdx.x >> g) & 1u) pm |= grp[4 + 8 * g + 3];
-        keyPairs[threadIdx.x] = pm;
+    /* the quads each key names.  Continuation ray (7 bits): the always-tested quads that are not shell quads, those of
+     * the groups whose bit is set, and the shell quads of the key's exit face (0..5 one face, 6 none, 7 all of them);
+     * shadow ray (the 4 group bits): the first two -- the shell quads are added when RT_KEY_SHELL asks for them */
+    uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1, *keyPairsS = keyPairs + NK;
+    if (threadIdx.x < NK) {
+        const uint32_t code = threadIdx.x & 7u, gb = threadIdx.x >> 3;
+        uint32_t pm = grp[RT_GRP_ALWAYS] & ~shellQuads;
+        for (uint32_t g = 0; g < K; g++) if ((gb >> g) & 1u) pm |= grp[4 + 8 * g + 3];
+        if (code == 0u) keyPairsS[gb] = pm;
+        keyPairs[threadIdx.x] = pm | (code < 6u ? grp[RT_GRP_FACES + code] : code == 6u ? 0u : shellQuads);
     }
     __syncthreads();
 
@@ -331,7 +336,9 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                         if (traceC) clear = clear && ray_clear_of_box(w, H, rd);
                         if (!clear) key |= 1u << g;
                     }
-                    /* can the shadow ray skip the shell quads?  (rt_scene_layout.h; sorted.cuh: shadow_inside_shell) */
+                    /* which face can the continuation ray leave the shell box through (the exit rule), and can the shadow ray
+                     * skip the shell quads?  (rt_scene_layout.h; sorted.cuh: exit_face_code, shadow_inside_shell) */
+                    key = (key << 3) | (traceC ? exit_face_code(shellBox, P, rd) : 6u);
                     SL.put_rays(slot, P, rd, traceC, color, sp.x, sp.z, id, key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
                 }
                 if (sort) {
@@ -345,34 +352,40 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
             /* -- S. counting sort of the slot numbers, keys descending -- */
             const uint16_t *order = hitlist;
             if (sort) {
-                uint32_t start;                                                /* lane j < 16: where key 15 - j starts */
+                /* where each key starts, keys descending: every warp works the same table out and writes it (same values) */
                 {
-                    const uint32_t c = lane < RT_SORT_KEYS ? cnts[RT_SORT_KEYS - 1u - lane] : 0u;
-                    uint32_t incl = c;
+                    constexpr uint32_t PER = NK / 32u;
+                    uint32_t c[PER], sum = 0u;
 #pragma unroll
-                    for (int d = 1; d < RT_SORT_KEYS; d <<= 1) {
+                    for (uint32_t q = 0; q < PER; q++) { c[q] = cnts[NK - 1u - (lane * PER + q)]; sum += c[q]; }
+                    uint32_t incl = sum;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
                         const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
                         if (lane >= (uint32_t)d) incl += up;
                     }
-                    start = incl - c;
+                    uint32_t at = incl - sum;
+#pragma unroll
+                    for (uint32_t q = 0; q < PER; q++) { startOf[NK - 1u - (lane * PER + q)] = at; at += c[q]; }
+                    __syncwarp();
                 }
 #pragma unroll 1
                 for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
                     const uint32_t e = c0 + lane;
                     const bool active = e < count;
                     const uint32_t slot = active ? hitlist[e] : 0u;
-                    const uint32_t key = active ? (SL.key(slot) & (RT_SORT_KEYS - 1u)) : 0xffu;
+                    const uint32_t key = active ? (SL.key(slot) & (NK - 1u)) : 0xffffu;
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
                     const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
                     uint32_t at = 0u;
                     if (active && lane == leader) at = atomicAdd(&run[key], (uint32_t)__popc(same));
-                    at = __shfl_sync(0xffffffffu, at, leader) + __shfl_sync(0xffffffffu, start, (RT_SORT_KEYS - 1u - key) & 31u);
+                    at = __shfl_sync(0xffffffffu, at, leader) + (active ? startOf[key] : 0u);
                     if (active) sorted[at + __popc(same & lt)] = (uint16_t)slot;
                 }
                 order = sorted;
             }
             __syncthreads();
-            if (sort && threadIdx.x < 2 * RT_SORT_KEYS) cnts[threadIdx.x] = 0u;   /* cnts and run, for the next bounce */
+            if (sort) for (uint32_t k = threadIdx.x; k < 2 * NK; k += RT_BLOCK_THREADS) cnts[k] = 0u;   /* cnts and run, for the next bounce */
 
             /* -- B. trace: chunks of the sorted list, a ticket each -- */
 #pragma unroll 1
@@ -389,9 +402,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 if (active) SL.get_trace_head(slot, colorHead, surf, key);
                 __syncwarp();                                                  /* (unsorted single chunk: its entries are read before the list is rewritten) */
                 const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
-                const uint32_t pairs = keyPairs[keys & (RT_SORT_KEYS - 1u)];
-                /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box */
-                const uint32_t pairsS = (keys & RT_KEY_SHELL) ? pairs : (pairs & ~shellQuads);
+                /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box;
+                 * the continuation rays take the union of the entries' lists (exit faces do not OR as the groups' bits do) */
+                const uint32_t pairsS = keyPairsS[(keys >> 3) & (RT_SORT_KEYS - 1u)] | ((keys & RT_KEY_SHELL) ? shellQuads : 0u);
+                const uint32_t pairs = __reduce_or_sync(0xffffffffu, active ? keyPairs[key & (NK - 1u)] : 0u) | pairsS;
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {

@@ -23,7 +23,8 @@
 
 #define RT_MAX_GROUPS 4
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
-#define RT_GROUP_WORDS (RT_GRP_SHELL_BOX + 8)
+#define RT_GRP_FACES (RT_GRP_SHELL_BOX + 8)
+#define RT_GROUP_WORDS (RT_GRP_FACES + 8)
 
 extern void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
                                     int hit, float distance, uint32_t primitive_id);
@@ -107,7 +108,15 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
         float *r = (float *)out + RT_GRP_SHELL_BOX;
         const float shrink = ext * (1.0f / 16384.0f);
         for (int k = 0; k < 3; k++) { r[k] = (alo[k] + ahi[k]) * 0.5f; r[4 + k] = (ahi[k] - alo[k]) * 0.5f - shrink; }
-        r[7] = shrink;
+        r[7] = shrink; r[3] = margin;
+        /* the shell quads face by face (the exit rule, rt_scene_layout.h) */
+        for (uint32_t p = 0; p < P; p++)
+            if ((shell >> p) & 1u)
+                for (int k = 0; k < 3; k++)
+                    if (lo[p][k] == hi[p][k]) {
+                        if (lo[p][k] == alo[k]) out[RT_GRP_FACES + 2 * k] |= 1u << p;
+                        if (lo[p][k] == ahi[k]) out[RT_GRP_FACES + 2 * k + 1] |= 1u << p;
+                    }
     }
     out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u; out[3] = shell;
     return (int)K;
@@ -132,6 +141,32 @@ static struct {
 } g_chk;
 static _Thread_local int t_pending; static _Thread_local float t_origin[3]; static _Thread_local uint32_t t_key;
 
+/* the exit rule (rt_scene_layout.h; csrc/sortedblk.cuh: exit_face_code): the shell quads a closest-hit ray from o along d
+ * must still be tested against.  (The kernel multiplies by an approximate reciprocal where this divides: its crossing points
+ * differ in the seventh digit, the margin is 1/128 of the scene.) */
+static uint32_t exit_rule(const float o[3], const float d[3]) {
+    const float *bx = (const float *)g_chk.words + RT_GRP_SHELL_BOX;
+    const uint32_t shell = g_chk.words[3];
+    for (int k = 0; k < 3; k++)
+        if (!(fabsf(o[k] - bx[k]) < bx[4 + k])) return shell;               /* starts outside the shrunk box: all of them */
+    uint32_t out = 0; int n = 0;
+    for (int k = 0; k < 3; k++) {
+        if (d[k] == 0.0f) continue;                                          /* parallel to both faces of the axis */
+        const int hiSide = d[k] > 0.0f;
+        const float hu = bx[4 + k] + bx[7];
+        const float b = hiSide ? bx[k] + hu : bx[k] - hu;
+        const float t = (b - o[k]) / d[k];
+        int in = 1;
+        for (int j = 0; j < 3; j++) {
+            if (j == k) continue;
+            const float pj = fmaf(t, d[j], o[j]);
+            if (fabsf(pj - bx[j]) > bx[4 + j] + bx[7] + bx[3]) in = 0;       /* (a NaN keeps the face) */
+        }
+        if (in) { out |= g_chk.words[RT_GRP_FACES + 2 * k + hiSide]; n++; }
+    }
+    return n > 1 ? shell : out;                                              /* the kernel's key has room for one face, none or all */
+}
+
 static void cull_hook(const float o[3], const float d[3], float tmin, float tmax, int any,
                       int hit, float distance, uint32_t primitive_id) {
     const uint32_t K = g_chk.words[0];
@@ -141,6 +176,7 @@ static void cull_hook(const float o[3], const float d[3], float tmin, float tmax
         const float w[3] = { r[0] - o[0], r[1] - o[1], r[2] - o[2] };
         if (!ray_clear_of_box(w, r + 4, d)) { key |= 1u << g; pairs |= g_chk.words[4 + 8 * g + 3]; }
     }
+    if (!any) pairs = (pairs & ~g_chk.words[3]) | exit_rule(o, d);
     if (any) {
         /* the shell rule: both ends of the shadow ray inside the shrunk box of the always-tested quads' bounds */
         const float *bx = (const float *)g_chk.words + RT_GRP_SHELL_BOX, *sp = rt_oracle_light_sample;

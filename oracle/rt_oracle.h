@@ -99,8 +99,8 @@ void rt_fixture_spheres(int width, int height, uint32_t seed, uint32_t numSphere
 void rt_fixture_offsets(uint32_t *offsets, int width, int row0, int rows, uint32_t seed);
 
 /* ---- object groups of the sorted kernel (rt_groups.c) ------------------------ */
-/* out: the 36 words of the prepared scene's "group" section (csrc/rt_scene_layout.h); returns K */
-int  rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L, uint32_t out[44]);
+/* out: the 52 words of the prepared scene's "group" section (csrc/rt_scene_layout.h); returns K */
+int  rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L, uint32_t out[52]);
 /* traces the frame and repeats every ray query against the quads group culling leaves: stats = queries,
  * mismatches (must be 0), triangle tests with / without culling, keysDual[16], keysSingle[16] */
 int  rt_oracle_cullcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,

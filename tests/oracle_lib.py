@@ -138,8 +138,8 @@ def sgridcheck(scene, width, height, spp, *, bounces=3, seed=1, y0=0, y1=None, n
 
 
 def groups(scene):
-    """The 44 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
-    out = np.zeros(44, np.uint32)
+    """The 52 words of the prepared scene's "group" section, restated on the CPU (oracle/rt_groups.c)."""
+    out = np.zeros(52, np.uint32)
     lib.rt_oracle_groups(vp(scene["vertices"]), C.c_uint32(scene["T"]), vp(scene["lights"]), C.c_uint32(scene["L"]), vp(out))
     return out
 

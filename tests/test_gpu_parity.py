@@ -580,7 +580,7 @@ def test_device_object_groups_match_the_cpu_restatement(dev):
         v32 = sc["vertices"].view(np.uint32)
         paired = all(np.array_equal(v32[(3 * i) * 4:(3 * i) * 4 + 3], v32[(3 * (i - 1)) * 4:(3 * (i - 1)) * 4 + 3]) for i in range(1, T, 2))
         inp = np.concatenate([np.array([T, Lc, int(paired), 0], np.uint32).view(np.uint8), sc["vertices"], sc["lights"]])
-        got = debug_eval(dev, 6, inp, np.zeros(44, np.uint32))
+        got = debug_eval(dev, 6, inp, np.zeros(52, np.uint32))
         want = O.groups(sc)
         assert np.array_equal(got, want), (got, want)
 
