@@ -501,7 +501,7 @@ __device__ __forceinline__ void pathtrace_sorted_body(const float *__restrict__ 
                 const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
                 const uint32_t pairs = keyPairs[keys & (RT_SORT_KEYS - 1u)];
                 /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box */
-                const uint32_t pairsS = (keys & RT_KEY_SHELL) ? pairs : (pairs & ~shellQuads);
+                const uint32_t pairsS = ((keys & RT_KEY_SHELL) ? pairs : (pairs & ~shellQuads)) & ~grp[RT_GRP_LIGHT_PLANE];
                 bool alive = false;
                 uint32_t id = 0;
                 if (active) {

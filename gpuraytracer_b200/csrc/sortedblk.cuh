@@ -142,7 +142,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
         const uint32_t code = threadIdx.x & 7u, gb = threadIdx.x >> 3;
         uint32_t pm = grp[RT_GRP_ALWAYS] & ~shellQuads;
         for (uint32_t g = 0; g < K; g++) if ((gb >> g) & 1u) pm |= grp[4 + 8 * g + 3];
-        if (code == 0u) keyPairsS[gb] = pm;
+        if (code == 0u) keyPairsS[gb] = pm & ~grp[RT_GRP_LIGHT_PLANE];     /* (the light's own quads: rt_scene_layout.h) */
         keyPairs[threadIdx.x] = pm | (code < 6u ? grp[RT_GRP_FACES + code] : code == 6u ? 0u : shellQuads);
     }
     __syncthreads();

@@ -24,12 +24,14 @@
 #define RT_MAX_GROUPS 4
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_FACES (RT_GRP_SHELL_BOX + 8)
+#define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)
 #define RT_GROUP_WORDS (RT_GRP_FACES + 8)
 
 extern void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
                                     int hit, float distance, uint32_t primitive_id);
 extern _Thread_local float rt_oracle_light_sample[3];     /* rt_oracle.c: the sample point the shadow ray aims at */
 
+static const int g_light_normals_bound = 0;      /* (the library builds no groups' mask when a light-normal table is bound; the checker never binds one here) */
 int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L,
                      uint32_t out[RT_GROUP_WORDS]) {
     const float *v = (const float *)vertices;
@@ -118,6 +120,12 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
                         if (lo[p][k] == ahi[k]) out[RT_GRP_FACES + 2 * k + 1] |= 1u << p;
                     }
     }
+    /* the quads in the plane of the one light: no shadow ray can be accepted by them (rt_scene_layout.h) */
+    if (L == 1 && ext < 64.0f && !g_light_normals_bound) {
+        const float cy = ((const float *)&lights[0].center)[1];
+        for (uint32_t p = 0; p < P; p++)
+            if (lo[p][1] == cy && hi[p][1] == cy) out[RT_GRP_LIGHT_PLANE] |= 1u << p;
+    }
     out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u; out[3] = shell;
     return (int)K;
 }
@@ -183,6 +191,7 @@ static void cull_hook(const float o[3], const float d[3], float tmin, float tmax
         int in = 1;
         for (int k = 0; k < 3; k++) in = in && fabsf(o[k] - bx[k]) < bx[4 + k] && fabsf(sp[k] - bx[k]) < bx[4 + k];
         if (in) pairs &= ~g_chk.words[3];
+        pairs &= ~g_chk.words[RT_GRP_LIGHT_PLANE];
 #pragma omp atomic
         g_chk.shadowQueries++;
         if (in) {
