@@ -78,6 +78,7 @@ __device__ __forceinline__ bool dual_hit_pairs(const SceneRef<false> &sc, uint32
         if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
 #pragma unroll
         for (uint32_t h = 0; h < 2; h++) {
+            if (h == 1 && pb == pa) break;                                         /* an odd last quad: alone (warp-uniform) */
             const uint32_t t0 = 2u * (h ? pb : pa);
             f3 w = mk(0.0f, 0.0f, 0.0f), cC = w, cS = w;
 #pragma unroll
@@ -123,6 +124,7 @@ __device__ __forceinline__ bool dual_hit_pairs_masked(const SceneRef<false> &sc,
         if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
 #pragma unroll
         for (uint32_t h = 0; h < 2; h++) {
+            if (h == 1 && pb == pa) break;                                         /* an odd last quad: alone (warp-uniform) */
             const uint32_t q = h ? pb : pa, t0 = 2u * q;
             const bool doS = (pairsS >> q) & 1u;                                   /* warp-uniform */
             f3 w = mk(0.0f, 0.0f, 0.0f), cC = w, cS = w;
@@ -166,6 +168,7 @@ __device__ __forceinline__ bool closest_hit_pairs(const SceneRef<false> &sc, uin
         if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
 #pragma unroll
         for (uint32_t h = 0; h < 2; h++) {
+            if (h == 1 && pb == pa) break;                                         /* an odd last quad: alone (warp-uniform) */
             const uint32_t t0 = 2u * (h ? pb : pa);
             f3 w = mk(0.0f, 0.0f, 0.0f), c = w;
 #pragma unroll
@@ -229,6 +232,7 @@ __device__ __forceinline__ bool any_hit_pairs(const SceneRef<false> &sc, uint32_
         if (pairs) { pb = (uint32_t)__ffs((int)pairs) - 1u; pairs &= pairs - 1u; }
 #pragma unroll
         for (uint32_t h = 0; h < 2; h++) {
+            if (h == 1 && pb == pa) break;                                         /* an odd last quad: alone (warp-uniform) */
             const uint32_t t0 = 2u * (h ? pb : pa);
             f3 w = mk(0.0f, 0.0f, 0.0f), c = w;
 #pragma unroll

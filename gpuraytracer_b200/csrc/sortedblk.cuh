@@ -15,6 +15,10 @@
  */
 #pragma once
 
+#ifndef RT_EXP_TICKET_AHEAD
+#define RT_EXP_TICKET_AHEAD 1  /* A/B (tools/build_exp.sh): 1 = pass B draws the next chunk's ticket before tracing the current chunk */
+#endif
+
 /* The slots of a block's round, in either layout of rt_kernel_smem.h (RT_SORTBLK_F4).  What a slot holds over a bounce:
  * camera phase / pass B leave the hit point X and the surface id; pass A turns X into P and adds the continuation
  * direction D, the throughput colour, x and z of the light sample point and the sort key; pass B reads all of it. */
@@ -388,12 +392,24 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
             if (sort) for (uint32_t k = threadIdx.x; k < 2 * NK; k += RT_BLOCK_THREADS) cnts[k] = 0u;   /* cnts and run, for the next bounce */
 
             /* -- B. trace: chunks of the sorted list, a ticket each -- */
+            /* (the next chunk's ticket is drawn before this chunk is traced: RT_EXP_TICKET_AHEAD) */
+            uint32_t cNext = 0u;
+            if (RT_EXP_TICKET_AHEAD) {
+                if (lane == 0) cNext = atomicAdd(&ctr[3], 1u) * 32u;
+                cNext = __shfl_sync(0xffffffffu, cNext, 0);
+            }
 #pragma unroll 1
             for (;;) {
                 uint32_t c0 = 0u;
-                if (lane == 0) c0 = atomicAdd(&ctr[3], 1u) * 32u;
-                c0 = __shfl_sync(0xffffffffu, c0, 0);
-                if (c0 >= count) break;
+                if (RT_EXP_TICKET_AHEAD) {
+                    c0 = cNext;
+                    if (c0 >= count) break;
+                    if (lane == 0) cNext = atomicAdd(&ctr[3], 1u) * 32u;
+                } else {
+                    if (lane == 0) c0 = atomicAdd(&ctr[3], 1u) * 32u;
+                    c0 = __shfl_sync(0xffffffffu, c0, 0);
+                    if (c0 >= count) break;
+                }
                 const uint32_t e = c0 + lane;
                 const bool active = e < count;
                 const uint32_t slot = active ? order[e] : 0u;
@@ -476,6 +492,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 if (alive) {
                     hitlist[base + __popc(mask & lt)] = (uint16_t)slot;
                 }
+                if (RT_EXP_TICKET_AHEAD) cNext = __shfl_sync(0xffffffffu, cNext, 0);
             }
             __syncthreads();
             count = ctr[2];
