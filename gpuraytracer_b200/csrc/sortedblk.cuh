@@ -15,6 +15,9 @@
  */
 #pragma once
 
+#ifndef RT_EXP_SORT_UNROLL
+#define RT_EXP_SORT_UNROLL 2   /* A/B (profiles/r04x_ab.log: 1: 55.54 ms, 2: 55.09, 3: 55.35 at 256 spp): iterations of the rank loop in flight (a chain of dependent shared-memory round trips each) */
+#endif
 #ifndef RT_EXP_TICKET_AHEAD
 #define RT_EXP_TICKET_AHEAD 1  /* A/B (tools/build_exp.sh): 1 = pass B draws the next chunk's ticket before tracing the current chunk */
 #endif
@@ -115,6 +118,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     uint8_t *idarr = (uint8_t *)(sorted + NSLOT), *keyarr = idarr + NSLOT;              /* (not there with F4: id and key live in the slot) */
     uint32_t *offs = F4 ? (uint32_t *)(sorted + NSLOT) : (uint32_t *)(keyarr + NSLOT);
     const SlotStore<NSLOT, F4> SL = { Q, idarr, keyarr };
+    constexpr int SORT_UNROLL = RT_EXP_SORT_UNROLL;
     constexpr uint32_t NK = RT_SORTBLK_KEYS;           /* sort keys: exit face (3 bits) under the groups' bits; bit 7 of a key byte is RT_KEY_SHELL */
     uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + NK, *startOf = run + NK;
     uint32_t *ctr = startOf + NK;                      /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
@@ -373,7 +377,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     for (uint32_t q = 0; q < PER; q++) { startOf[NK - 1u - (lane * PER + q)] = at; at += c[q]; }
                     __syncwarp();
                 }
-#pragma unroll 1
+#pragma unroll SORT_UNROLL
                 for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
                     const uint32_t e = c0 + lane;
                     const bool active = e < count;
