@@ -16,6 +16,12 @@
 #define RT_SORT_FIELDS  11      /* sorted.cuh slot: X.xyz (hit point, then P)  D.xyz  colour.xyz  light sample x, z   */
 #define RT_SORT_KEYS    (1 << RT_MAX_GROUPS)
 #define RT_SORTBLK_KEYS (8 << RT_MAX_GROUPS)   /* sortedblk.cuh: the groups' bits above three bits of exit face (rt_scene_layout.h) */
+/* ... except in the wide form (a block lives for ONE round there and four blocks fit an SM only without the 1.3 KB the
+ * longer tables take: profiles/r04z_c5_*.csv, three blocks: 0.338 ms a frame against 0.326), which keeps the groups' keys */
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+constexpr uint32_t rtSortedBlkKeys(bool wide) { return wide ? (uint32_t)RT_SORT_KEYS : (uint32_t)RT_SORTBLK_KEYS; }
 
 #if defined(__CUDACC__)
 #define RT_CX __host__ __device__ constexpr
@@ -51,9 +57,9 @@ RT_CX uint32_t rtSortedBlkSlots(uint32_t R) { return RT_BLOCK_WARPS * 32u * R; }
 RT_CX uint32_t rtSortedBlkCoreWords(uint32_t R, bool wide) {
     return (RT_SORTBLK_F4 ? 15u * rtSortedBlkSlots(R) + (4u * rtSortedBlkSlots(R)) / 4u
                           : (RT_SORT_FIELDS + 3u) * rtSortedBlkSlots(R) + (6u * rtSortedBlkSlots(R)) / 4u) +
-           (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) + 3u * RT_SORTBLK_KEYS + 4u;
+           (wide ? rtSortedBlkSlots(R) : RT_BLOCK_WARPS * 32u) + 3u * rtSortedBlkKeys(wide) + 4u;
 }
 /* (after the core: candidate bits, unit word, the key -> quads tables of the continuation ray and of the shadow ray) */
-RT_CX uint32_t rtSortedBlkWords(uint32_t R, bool wide, uint32_t T) { return rtSortedBlkCoreWords(R, wide) + rtCullWords(T, 0u) + RT_SORTBLK_KEYS + RT_SORT_KEYS; }
+RT_CX uint32_t rtSortedBlkWords(uint32_t R, bool wide, uint32_t T) { return rtSortedBlkCoreWords(R, wide) + rtCullWords(T, 0u) + rtSortedBlkKeys(wide) + RT_SORT_KEYS; }
 
 #endif

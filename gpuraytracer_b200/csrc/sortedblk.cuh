@@ -92,7 +92,7 @@ struct SortBlkSmem {
      * the Halton index of every slot instead of one offset per lane */
     static constexpr uint32_t OFFS = SPATIAL ? NSLOT : RT_BLOCK_THREADS;
     static constexpr uint32_t WORDS = rtSortedBlkCoreWords(R, SPATIAL);        /* rt_kernel_smem.h: what the host launches with */
-    static_assert(WORDS == (RT_SORTBLK_F4 ? 15u * NSLOT + NSLOT : (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u) + OFFS + 3u * RT_SORTBLK_KEYS + 4u, "layout below");
+    static_assert(WORDS == (RT_SORTBLK_F4 ? 15u * NSLOT + NSLOT : (RT_SORT_FIELDS + 3u) * NSLOT + (6u * NSLOT) / 4u) + OFFS + 3u * rtSortedBlkKeys(SPATIAL) + 4u, "layout below");
 };
 
 template <int R, bool PERSIST, bool SPATIAL = false, bool MIS = false>
@@ -119,7 +119,9 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
     uint32_t *offs = F4 ? (uint32_t *)(sorted + NSLOT) : (uint32_t *)(keyarr + NSLOT);
     const SlotStore<NSLOT, F4> SL = { Q, idarr, keyarr };
     constexpr int SORT_UNROLL = RT_EXP_SORT_UNROLL;
-    constexpr uint32_t NK = RT_SORTBLK_KEYS;           /* sort keys: exit face (3 bits) under the groups' bits; bit 7 of a key byte is RT_KEY_SHELL */
+    /* sort keys: exit face (CB = 3 bits; none in the wide form, rt_kernel_smem.h) under the groups' bits; bit 7 of a key byte is RT_KEY_SHELL */
+    constexpr bool EXIT = !SPATIAL;
+    constexpr uint32_t NK = rtSortedBlkKeys(SPATIAL), CB = EXIT ? 3u : 0u;
     uint32_t *cnts = offs + SortBlkSmem<R, SPATIAL>::OFFS, *run = cnts + NK, *startOf = run + NK;
     uint32_t *ctr = startOf + NK;                      /* [0], [1] camera survivors of even / odd rounds  [2] survivors of a bounce  [3] chunk ticket */
     for (uint32_t k = threadIdx.x; k < 3 * NK + 4; k += RT_BLOCK_THREADS) cnts[k] = 0u;
@@ -147,10 +149,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
      * shadow ray (the 4 group bits): the first two -- the shell quads are added when RT_KEY_SHELL asks for them */
     uint32_t *keyPairs = tail + (RT_BLOCK_THREADS / 32) * mwT + 1, *keyPairsS = keyPairs + NK;
     if (threadIdx.x < NK) {
-        const uint32_t code = threadIdx.x & 7u, gb = threadIdx.x >> 3;
+        const uint32_t code = EXIT ? threadIdx.x & 7u : 7u, gb = threadIdx.x >> CB;
         uint32_t pm = grp[RT_GRP_ALWAYS] & ~shellQuads;
         for (uint32_t g = 0; g < K; g++) if ((gb >> g) & 1u) pm |= grp[4 + 8 * g + 3];
-        if (code == 0u) keyPairsS[gb] = pm & ~grp[RT_GRP_LIGHT_PLANE];     /* (the light's own quads: rt_scene_layout.h) */
+        if (!EXIT || code == 0u) keyPairsS[gb] = pm & ~grp[RT_GRP_LIGHT_PLANE];     /* (the light's own quads: rt_scene_layout.h) */
         keyPairs[threadIdx.x] = pm | (code < 6u ? grp[RT_GRP_FACES + code] : code == 6u ? 0u : shellQuads);
     }
     __syncthreads();
@@ -346,7 +348,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     }
                     /* which face can the continuation ray leave the shell box through (the exit rule), and can the shadow ray
                      * skip the shell quads?  (rt_scene_layout.h; sorted.cuh: exit_face_code, shadow_inside_shell) */
-                    key = (key << 3) | (traceC ? exit_face_code(shellBox, P, rd) : 6u);
+                    if (EXIT) key = (key << 3) | (traceC ? exit_face_code(shellBox, P, rd) : 6u);
                     SL.put_rays(slot, P, rd, traceC, color, sp.x, sp.z, id, key | (shadow_inside_shell(shellBox, P, sp) ? 0u : RT_KEY_SHELL));
                 }
                 if (sort) {
@@ -362,10 +364,10 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
             if (sort) {
                 /* where each key starts, keys descending: every warp works the same table out and writes it (same values) */
                 {
-                    constexpr uint32_t PER = NK / 32u;
+                    constexpr uint32_t PER = (NK + 31u) / 32u;
                     uint32_t c[PER], sum = 0u;
 #pragma unroll
-                    for (uint32_t q = 0; q < PER; q++) { c[q] = cnts[NK - 1u - (lane * PER + q)]; sum += c[q]; }
+                    for (uint32_t q = 0; q < PER; q++) { c[q] = lane * PER + q < NK ? cnts[NK - 1u - (lane * PER + q)] : 0u; sum += c[q]; }
                     uint32_t incl = sum;
 #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
@@ -374,7 +376,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     }
                     uint32_t at = incl - sum;
 #pragma unroll
-                    for (uint32_t q = 0; q < PER; q++) { startOf[NK - 1u - (lane * PER + q)] = at; at += c[q]; }
+                    for (uint32_t q = 0; q < PER; q++) { if (lane * PER + q < NK) startOf[NK - 1u - (lane * PER + q)] = at; at += c[q]; }
                     __syncwarp();
                 }
 #pragma unroll SORT_UNROLL
@@ -424,7 +426,7 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 const uint32_t keys = __reduce_or_sync(0xffffffffu, key);
                 /* the shadow rays skip the shell quads unless an entry of the chunk starts or ends outside the shell box;
                  * the continuation rays take the union of the entries' lists (exit faces do not OR as the groups' bits do) */
-                const uint32_t pairsS = keyPairsS[(keys >> 3) & (RT_SORT_KEYS - 1u)] | ((keys & RT_KEY_SHELL) ? shellQuads : 0u);
+                const uint32_t pairsS = keyPairsS[(keys >> CB) & (RT_SORT_KEYS - 1u)] | ((keys & RT_KEY_SHELL) ? shellQuads : 0u);
                 const uint32_t pairs = __reduce_or_sync(0xffffffffu, active ? keyPairs[key & (NK - 1u)] : 0u) | pairsS;
                 bool alive = false;
                 uint32_t id = 0;
