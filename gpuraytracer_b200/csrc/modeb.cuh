@@ -70,47 +70,69 @@ __device__ __forceinline__ float power_heuristic(float pdf1, float pdf2, float p
 #else
 #define RT_MODEB_FN __forceinline__
 #endif
-__device__ RT_MODEB_FN f3 brdf_contribution(const SurfB &s, f3 l) {
-    f3 v = -normalize(s.rdir);
+/* What the BRDF, the VNDF pdf and the light pdf need of the SURFACE alone: the three strategy loops evaluate them 300 times
+ * for one camera-ray surface (the compiler cannot hoist this out of an out-of-line function), the next-event estimate at the
+ * second vertex once for its own.  Same operations on the same operands as the one-piece forms of the shader. */
+struct SurfPre {
+    f3 v; float NoV;                    /* :260, :263  -normalize(ray.direction), |n.v| + 1e-5 */
+    f3 f0, omf0, Fd; float omMetal;     /* :268, :271 (1 - f0), :277, :280 (1 - metallic) */
+    float sV;                           /* :206  sqrt((-NoV a2 + NoV) NoV + a2) of V_SmithGGXCorrelated */
+    float pdfNoV, G1;                   /* :440, :442  |n.viewDir| with viewDir = -ray.direction as it is, smithG1 of it */
+    float dist2;                        /* :317-318, :324  distance * distance to the light's centre */
+};
+__device__ __forceinline__ void surf_pre_brdf(const SurfB &s, SurfPre &q) {
+    q.v = -normalize(s.rdir);
+    q.NoV = fabsf(dot(s.normal, q.v)) + 1e-5f;
+    f3 d0 = mk(0.04f, 0.04f, 0.04f);
+    q.f0 = d0 + (s.diffuse - d0) * s.metallic;
+    q.omf0 = mk(1.0f, 1.0f, 1.0f) - q.f0;
+    q.Fd = s.diffuse * (1.0f / RT_PI_F);
+    q.omMetal = 1.0f - s.metallic;
+    float a2 = s.roughness * s.roughness;
+    q.sV = sqrtf((-q.NoV * a2 + q.NoV) * q.NoV + a2);
+}
+__device__ __forceinline__ void surf_pre_pdfs(const SurfB &s, const LightB &L, SurfPre &q) {
+    q.pdfNoV = fabsf(dot(s.normal, -s.rdir));
+    q.G1 = smithG1_GGX(q.pdfNoV, s.roughness);
+    float distance = length(L.center - s.point);
+    q.dist2 = distance * distance;
+}
+__device__ RT_MODEB_FN f3 brdf_contribution(const SurfB &s, const SurfPre &q, f3 l) {
     f3 n = s.normal;
-    f3 h = normalize(v + l);
-    float NoV = fabsf(dot(n, v)) + 1e-5f;
+    f3 h = normalize(q.v + l);
+    float NoV = q.NoV;
     float NoL = fminf(1.0f, fmaxf(0.0f, dot(n, l)));
     float NoH = fminf(1.0f, fmaxf(0.0f, dot(n, h)));
     float LoH = fminf(1.0f, fmaxf(0.0f, dot(l, h)));
-    f3 d0 = mk(0.04f, 0.04f, 0.04f);
-    f3 f0 = d0 + (s.diffuse - d0) * s.metallic;
     float D = D_GGX(NoH, s.roughness);
-    f3 F = f0 + (mk(1.0f, 1.0f, 1.0f) - f0) * pow_det(1.0f - LoH, 5.0f);          /* F_Schlick :199-201 */
-    float G = V_SmithGGXCorrelated(NoV, NoL, s.roughness);
+    f3 F = q.f0 + q.omf0 * pow_det(1.0f - LoH, 5.0f);                             /* F_Schlick :199-201 */
+    float a2 = s.roughness * s.roughness;                                         /* V_SmithGGXCorrelated :203-208 */
+    float GGXL = NoV * sqrtf((-NoL * a2 + NoL) * NoL + a2);
+    float GGXV = NoL * q.sV;
+    float G = 0.5f / (GGXV + GGXL);
     f3 Fr = (F * (D * G)) / (4.0f * NoV * NoL + 1e-7f);
-    f3 Fd = s.diffuse * (1.0f / RT_PI_F);
-    f3 kD = (mk(1.0f, 1.0f, 1.0f) - F) * (1.0f - s.metallic);
-    f3 BRDF = kD * (Fd + Fr);
+    f3 kD = (mk(1.0f, 1.0f, 1.0f) - F) * q.omMetal;
+    f3 BRDF = kD * (q.Fd + Fr);
     return BRDF * NoL;
 }
 
-/* :315-326 */
-__device__ __forceinline__ float square_light_pdf(f3 origin, const LightB &L, f3 direction) {
-    f3 toLight = L.center - origin;
-    float distance = length(toLight);
+/* :315-326 (dist2: SurfPre) */
+__device__ __forceinline__ float square_light_pdf(float dist2, const LightB &L, f3 direction) {
     float cosTheta = fmaxf(0.0f, dot(-direction, mk(0.0f, -1.0f, 0.0f)));
     float area = L.width * L.depth;
-    return (distance * distance) / (area * cosTheta + 1e-6f);
+    return dist2 / (area * cosTheta + 1e-6f);
 }
 /* :376-380 */
 __device__ __forceinline__ float cosine_pdf(f3 normal, f3 direction) {
     return fmaxf(0.0f, dot(normal, direction)) / RT_PI_F;
 }
-/* :436-445 */
-__device__ __forceinline__ float vndf_pdf(f3 viewDir, f3 normal, f3 lightDir, float roughness) {
+/* :436-445 (NoV and G1: SurfPre) */
+__device__ __forceinline__ float vndf_pdf(f3 viewDir, f3 normal, f3 lightDir, float roughness, const SurfPre &q) {
     f3 h = normalize(viewDir + lightDir);
     float NoH = fabsf(dot(normal, h));
     float VoH = fabsf(dot(viewDir, h));
-    float NoV = fabsf(dot(normal, viewDir));
     float D = D_GGX(NoH, roughness);
-    float G1 = smithG1_GGX(NoV, roughness);
-    return (D * G1 * VoH) / (4.0f * NoV);
+    return (D * q.G1 * VoH) / (4.0f * q.pdfNoV);
 }
 
 /* :355-374: direction only (origin, min 0.001, max 1000 are fixed) */
@@ -205,8 +227,8 @@ __device__ __forceinline__ bool load_surface(const float *sm, const RTSceneLayou
 
 /* calculateDirectLightSamplingContribution, :519-541 (directSquareLightRay :291-313 inlined) */
 __device__ RT_MODEB_FN f3 direct_light(const float *sm, const RTSceneLayout &lay, const float4 *base, uint32_t T4,
-                                           const LightB &L, const SurfB &s, float rx, float ry, float n, bool usePower,
-                                           uint32_t &rays) {
+                                           const LightB &L, const SurfB &s, const SurfPre &q, float rx, float ry, float n,
+                                           bool usePower, uint32_t &rays) {
     f3 origin = s.point + s.normal * 1e-4f;
     float x = (rx - 0.5f) * L.width;
     float y = (ry - 0.5f) * L.depth;
@@ -218,11 +240,11 @@ __device__ RT_MODEB_FN f3 direct_light(const float *sm, const RTSceneLayout &lay
     rays++;
     if (!closest_b(base, sm + lay.group, T4, lay.T, origin, ldir, 0.001f, distance, true, samplePos, dist, id)) return mk(0.0f, 0.0f, 0.0f);
     if (sm[lay.shade + id + RT_SH_FLAG * lay.Tp] == 0.0f) return mk(0.0f, 0.0f, 0.0f);       /* not HitLight */
-    f3 brdf = brdf_contribution(s, ldir);
-    float directLightPDF = square_light_pdf(s.point, L, ldir);
+    f3 brdf = brdf_contribution(s, q, ldir);
+    float directLightPDF = square_light_pdf(q.dist2, L, ldir);
     if (usePower) {
         float cosinePDF = cosine_pdf(s.normal, ldir);
-        float vndfPDF = vndf_pdf(-s.rdir, s.normal, ldir, s.roughness);
+        float vndfPDF = vndf_pdf(-s.rdir, s.normal, ldir, s.roughness, q);
         float weight = power_heuristic(directLightPDF, cosinePDF, vndfPDF, n);
         return ((brdf * weight) * L.er) / directLightPDF;
     }
@@ -315,11 +337,14 @@ drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, f
         /* recursiveMultiImportanceSampling, :543-625: three strategies, one rolled loop */
         const f3 origin = in.point + in.normal * 1e-4f;
         const f3 view = -in.rdir;
+        SurfPre pre;
+        surf_pre_brdf(in, pre);
+        surf_pre_pdfs(in, L, pre);
         f3 sumL = mk(0.0f, 0.0f, 0.0f), sumC = sumL, sumV = sumL;
 #pragma unroll 1
         for (uint32_t k = 0; k < sps; k++) {                                                   /* :553-560 */
             float2 u = tabL[k];
-            sumL = sumL + direct_light(sm, lay, base, T4, L, in, u.x, u.y, nf, true, rays);
+            sumL = sumL + direct_light(sm, lay, base, T4, L, in, pre, u.x, u.y, nf, true, rays);
         }
 #pragma unroll 1
         for (uint32_t k = 0; k < 2u * sps; k++) {                                              /* :562-591 and :593-623 */
@@ -328,15 +353,15 @@ drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, f
             float2 u = vndf ? tabV[j] : tabC[j];
             f3 dir = vndf ? vndf_dir(in, view, u.x, u.y) : cosine_weighted_dir(in, u.x, u.y);
             float cosinePDF = cosine_pdf(in.normal, dir);
-            float directLightPDF = square_light_pdf(in.point, L, dir);
-            float vndfPDF = vndf_pdf(view, in.normal, dir, in.roughness);
+            float directLightPDF = square_light_pdf(pre.dist2, L, dir);
+            float vndfPDF = vndf_pdf(view, in.normal, dir, in.roughness, pre);
             float ownPDF = vndf ? vndfPDF : cosinePDF;
             float weight = vndf ? power_heuristic(vndfPDF, directLightPDF, cosinePDF, nf)
                                 : power_heuristic(cosinePDF, directLightPDF, vndfPDF, nf);
             float d2; uint32_t id2;
             rays++;
             bool hit2 = closest_b(base, sm + lay.group, T4, lay.T, origin, dir, 0.001f, 1000.0f, false, origin, d2, id2);
-            f3 brdf = brdf_contribution(in, dir);
+            f3 brdf = brdf_contribution(in, pre, dir);
             f3 add = mk(0.0f, 0.0f, 0.0f);
             bool contributes = false;
             if (hit2) {
@@ -345,7 +370,11 @@ drawTriangle_mis(const float *__restrict__ scene, uchar4 *__restrict__ pixels, f
                     add = ((brdf * weight) * L.er) / ownPDF;
                 } else {                                                                        /* Hit: NEE at the second vertex */
                     float2 u2 = tab6[vndf ? j + sps : j];                                       /* haltonRandom(i, 6) / (i + sps, 6) */
-                    add = (brdf / ownPDF) * direct_light(sm, lay, base, T4, L, s2, u2.x, u2.y, 1.0f, false, rays);
+                    SurfPre pre2;                                                               /* (the pdfs' part is not used without the power heuristic) */
+                    surf_pre_brdf(s2, pre2);
+                    pre2.pdfNoV = 0.0f; pre2.G1 = 0.0f;
+                    { float distance = length(L.center - s2.point); pre2.dist2 = distance * distance; }
+                    add = (brdf / ownPDF) * direct_light(sm, lay, base, T4, L, s2, pre2, u2.x, u2.y, 1.0f, false, rays);
                 }
                 contributes = true;
             }
