@@ -715,3 +715,29 @@ def test_light_extent_flag_every_kernel_form(dev):
     gsc.vertices, gsc.materials, gsc.num_triangles = tv.copy(), tm.copy(), T
     ref, _ = O.pathtrace(osc, W3, H3, 4, light_extent=True)
     assert np.array_equal(G.Renderer(gsc, W3, H3, device=dev).draw(spp=4, variant=X), ref)
+
+
+@pytest.mark.parametrize("mode", ["stretched", "flush"])
+def test_exit_and_light_plane_rules_in_other_rooms(dev, mode):
+    """The block-sorted kernel's exit rule and light-plane rule away from the Cornell room's round numbers: the scene under an
+    affine map with three factors, and the light raised into the ceiling's plane (tests/test_group_cull_cpu.py: other_room, the
+    CPU checker's side of the same scenes); a camera outside and one inside the room, every sorted form and the MIS twin."""
+    from test_group_cull_cpu import other_room
+    W, H, spp = 176, 120, 12
+    for cam in (None, (0.3, -0.4, 1.5)):
+        osc = other_room(W, H, mode)
+        if cam is not None:
+            c = osc["camera"].view(np.float32)
+            c[0:3] = cam; c[4:7] = (0.1, -0.1, -1.0); c[14] = 1.4
+        gsc = G.init_cornell_box(W, H)
+        gsc.vertices[:] = osc["vertices"].view(np.uint8); gsc.lights[:] = osc["lights"].view(np.uint8); gsc.camera[:] = osc["camera"].view(np.uint8)
+        ref, _ = O.pathtrace(osc, W, H, spp, bounces=4)
+        r = G.Renderer(gsc, W, H, device=dev)
+        base = r.draw(spp=spp, bounces=4, variant=L.VARIANT_SMEM)
+        assert np.array_equal(base, ref), (mode, cam)
+        for variant in (L.VARIANT_DEFAULT, L.VARIANT_SORTED, L.VARIANT_SORTED_BLOCK, L.VARIANT_SORTED_BLOCK_TILES):
+            img = r.draw(spp=spp, bounces=4, variant=variant)
+            assert np.array_equal(img, ref), (mode, cam, variant, int((img != ref).sum()))
+        refm, _ = O.pathtrace(osc, W, H, spp, bounces=4, mis=O.MIS)
+        assert np.array_equal(r.draw(spp=spp, bounces=4, variant=L.VARIANT_SORTED_BLOCK | L.VARIANT_MIS), refm), (mode, cam)
+        assert np.array_equal(r.draw(spp=3, bounces=4), O.pathtrace(osc, W, H, 3, bounces=4)[0]), (mode, cam)      # the wide form

@@ -118,3 +118,39 @@ def test_culling_never_changes_a_query_modeb_frame():
         assert r["queries"] > 400_000 and r["mismatches"] == 0
         assert r["culled_tests"] < 0.3 * r["full_tests"]
         assert r["seg_in_shell"] > 0.999 * r["seg_queries"] > 0
+
+
+def other_room(W, H, mode):
+    """The Cornell scene in another room: "stretched" = every vertex and the light scaled and shifted by an affine map with
+    three different factors (the room is no cube, nothing sits at a round number); "flush" = the light raised into the
+    ceiling's plane (the ceiling is then one of the quads in the light's plane, and coplanar with the light's own)."""
+    sc = O.cornell(W, H)
+    f = sc["vertices"].view(np.float32).reshape(-1, 4)
+    lt = sc["lights"].view(np.float32)
+    if mode == "stretched":
+        s = np.array([1.3, 0.7, 1.1], np.float32); t = np.array([0.4, 0.3, -0.6], np.float32)
+        f[:, :3] = f[:, :3] * s + t
+        lt[0:3] = lt[0:3] * s + t
+    else:
+        top = np.float32(2.5)
+        f[f[:, 1] == np.float32(2.49), 1] = top
+        lt[1] = top
+    return sc
+
+
+def test_exit_and_light_plane_rules_in_other_rooms():
+    W, H, spp = 160, 120, 6
+    for mode in ("stretched", "flush"):
+        sc = other_room(W, H, mode)
+        grp = O.groups(sc)
+        flush = mode == "flush"
+        # two boxes as groups; the shell: five walls -- and the light's quad when it lies in the ceiling's plane
+        assert int(grp[2]) == 1 and int(grp[0]) == 2 and bin(int(grp[3])).count("1") == (6 if flush else 5)
+        assert [bin(int(x)).count("1") for x in grp[44:50]] == [1, 1, 1, 2 if flush else 1, 1, 0]   # face by face; none in front
+        assert bin(int(grp[50])).count("1") == (2 if flush else 1)                # in the light's plane: its quad; the ceiling too when flush
+        for cam in (None, (0.3, -0.4, 1.5)):
+            if cam is not None:
+                c = sc["camera"].view(np.float32)
+                c[0:3] = cam; c[4:7] = (0.1, -0.1, -1.0); c[14] = 1.4
+            r = O.cullcheck(sc, W, H, spp, bounces=4)
+            assert r["queries"] > 250_000 and r["mismatches"] == 0, (mode, cam, r["mismatches"])
