@@ -92,7 +92,7 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
     for (uint32_t k = lane; k < RT_GROUP_WORDS; k += 32u) gu[k] = 0u;
     __syncwarp();
     const uint32_t P = lay.T / 2u;
-    if (!(paired && lay.T >= 2u && lay.T <= 64u && lay.S == 0u)) return;          /* warp-uniform */
+    if (!(paired && lay.T >= 2u && lay.T <= 64u)) return;                         /* warp-uniform */
     const bool has = lane < P;
     const float INF = __int_as_float(0x7f800000);
     float lo[3] = { INF, INF, INF }, hi[3] = { -INF, -INF, -INF };
@@ -184,7 +184,16 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
             r[4 + k] = shell ? (ahi[k] - alo[k]) * 0.5f - shrink : 0.0f;
         }
         r[3] = shell ? margin : 0.0f; r[7] = shell ? shrink : 0.0f;      /* (modeb.cuh asks the origin for a quarter of the shrink) */
-        gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = K >= 1u ? 1u : 0u; gu[RT_GRP_SHELL] = shell;
+        /* (a scene with spheres has its triangles grouped for the shell's sake only: the sorted kernels are not for it) */
+        gu[RT_GRP_K] = K; gu[RT_GRP_ALWAYS] = always; gu[RT_GRP_OK] = (K >= 1u && lay.S == 0u) ? 1u : 0u; gu[RT_GRP_SHELL] = shell;
+        /* does every light's sample rectangle lie inside the shrunk shell box?  (rt_scene_layout.h: RT_GRP_LIGHTS_IN) */
+        bool in = shell != 0u && !(lay.flags & RT_LAYOUT_LIGHT_NORMALS);
+        for (uint32_t l = 0; l < lay.L; l++) {
+            const float *c = (const float *)(lights + 64 * (size_t)l);
+            const float hx = fmaxf(0.25f, 0.5f * c[12]), hz = fmaxf(0.25f, 0.5f * c[13]);
+            in = in && fabsf(c[0] - r[0]) + hx < r[4] && fabsf(c[1] - r[1]) < r[5] && fabsf(c[2] - r[2]) + hz < r[6];
+        }
+        gu[RT_GRP_LIGHTS_IN] = in ? 1u : 0u;
     }
 }
 
@@ -303,7 +312,7 @@ extern "C" __global__ void rt_prep_scene(const unsigned char *__restrict__ camer
         if (tid < 32) s_adj[tid] = 0u;
         ok = __syncthreads_and(ok);
         if (tid == 0) ((uint32_t *)scene)[RT_HDR_PAIRED] = ok ? 1u : 0u;
-        const bool groupable = ok && lay.T >= 2u && lay.T <= 64u && lay.S == 0u;              /* block-uniform */
+        const bool groupable = ok && lay.T >= 2u && lay.T <= 64u;                             /* block-uniform */
         if (groupable) prep_adjacency(vertices, lay.T / 2u, (uint32_t)tid & 31u, (uint32_t)tid >> 5, (uint32_t)nth >> 5, s_adj);
         __syncthreads();
         if (tid < 32) prep_groups(vertices, lights, scene, lay, ok != 0, (uint32_t)tid, s_adj);
@@ -609,7 +618,7 @@ __device__ __forceinline__ bool dual_hit(const SceneRef<CONST_BANK> &sc, f3 o,
  */
 template <bool CONST_BANK, int UNROLL, int N>
 __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3 o, const f3 (&d)[N], const float (&tmax)[N],
-                                              bool (&shadowed)[N]) {
+                                              bool (&shadowed)[N], uint32_t skipPairs = 0u) {
     bool sh[N];
 #pragma unroll
     for (int r = 0; r < N; r++) sh[r] = false;
@@ -618,6 +627,7 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
 #pragma unroll
         for (uint32_t u = 0; u < UNROLL; u++) {
             const uint32_t i = i0 + u;
+            if (skipPairs && ((skipPairs >> ((i >> 1) & 31u)) & 1u)) continue;   /* shell triangles no shadow ray of this pass can be accepted by (warp-uniform; wave.cuh) */
             const float4 A = sc.ld(4 * i), B = sc.ld(4 * i + 1), C = sc.ld(4 * i + 2);
             const f3 v0 = mk(A.x, A.y, A.z), n = mk(A.w, B.x, B.y), e2 = mk(B.z, B.w, C.x), e1n = mk(C.y, C.z, C.w);
             const f3 w = v0 - o;
@@ -681,7 +691,7 @@ __device__ __forceinline__ void any_hit_multi(const SceneRef<CONST_BANK> &sc, f3
  */
 template <int UNROLL, int NS>
 __device__ __forceinline__ bool multi_hit(const SceneRef<false> &sc, f3 o, f3 dc, float tminC, float tmaxC, float &dist, uint32_t &id,
-                                          const f3 (&ds)[NS], const float (&tmaxS)[NS], bool (&shadowed)[NS]) {
+                                          const f3 (&ds)[NS], const float (&tmaxS)[NS], bool (&shadowed)[NS], uint32_t skipPairs = 0u) {
     float bestN = tmaxC, bestD = 1.0f;
     uint32_t best = 0xffffffffu;
     bool sh[NS];
@@ -702,6 +712,7 @@ __device__ __forceinline__ bool multi_hit(const SceneRef<false> &sc, f3 o, f3 dc
                 const f3 c = cross(dc, w);
                 if (tri_accept(D, Nn, dot(e2, c), dot(e1n, c), tminC, bestN, bestD, N, a)) { bestN = N; bestD = a; best = i; }
             }
+            if (skipPairs && ((skipPairs >> ((i >> 1) & 31u)) & 1u)) continue;   /* shell triangles: the continuation ray only (warp-uniform; wave.cuh) */
 #pragma unroll
             for (int r = 0; r < NS; r++) {
                 const float D = dot(ds[r], n);

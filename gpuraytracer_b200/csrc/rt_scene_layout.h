@@ -41,6 +41,11 @@
  *            the plane AT its sample point, at t = ldist up to 1e-6 x ldist, and the shadow test ends at ldist - 1e-3
  *            (raytrace.metal:81): such a quad cannot be accepted by any shadow ray of the scene and is left out of their
  *            lists (sortedblk.cuh, sorted.cuh).  Only scenes smaller than 64 units across get the mask.
+ *            RT_GRP_LIGHTS_IN: every light's sample rectangle (taken with the larger of its two possible half extents,
+ *            0.25 and half its width / depth; lights with a normal of their own: never) lies inside the shrunk shell box.
+ *            Then the shell rule needs the shading point alone: the kernels for several lights (wave.cuh) skip the shell
+ *            triangles for all shadow rays of a pass when every lane's point is inside.  The shell, its box and this
+ *            word are built for scenes with spheres too (K, the boxes and [2] are not used there: [2] stays 0).
  *            A shadow ray whose two ends both lie inside the shrunk box cannot be accepted by a shell quad (the
  *            segment stays 3e-4 x extent clear of its plane; the test's own error is 1e-6 x extent), so those
  *            any-hit tests are skipped (sortedblk.cuh / sorted.cuh, pass B).
@@ -105,7 +110,8 @@
 #define RT_GRP_SHELL      3
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_FACES     (RT_GRP_SHELL_BOX + 8)     /* 6 pair masks: the shell quads in face 2 * axis + (1 = high side) */
-#define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)      /* pair mask: quads in the plane of the (one) light; then a spare word */
+#define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)      /* pair mask: quads in the plane of the (one) light */
+#define RT_GRP_LIGHTS_IN   (RT_GRP_FACES + 7)      /* 1: the sample rectangle of EVERY light lies inside the shrunk shell box */
 #define RT_GROUP_WORDS   (RT_GRP_FACES + 8)
 
 /* constant-bank mirror of the intersection part: float4 slots (56 KB of the 64 KB bank) */

@@ -137,6 +137,8 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     const float resX = sm[RT_HDR_RES_X], resY = sm[RT_HDR_RES_Y];
     const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
     const bool paired = ((const uint32_t *)sm)[RT_HDR_PAIRED] != 0u;           /* quads cut in two: pathtrace.cu, PAIRED */
+    /* the shell quads the shadow rays of a several-lights pass may skip (0: none, or some light reaches out of the shell box) */
+    const uint32_t shellSkip = ((const uint32_t *)sm)[lay.group + RT_GRP_LIGHTS_IN] ? ((const uint32_t *)sm)[lay.group + RT_GRP_SHELL] : 0u;
     Counters cnt = { 0u, 0u, 0u };
     unsigned long long paths = 0ull;
 
@@ -364,20 +366,29 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                     if (MIS) lcol[r] = lcol[r] * misA_light_weight(L, P, normal, ldir[r]);
                                 }
                             }
+                            /* the shell rule for a pass of shadow rays (rt_scene_layout.h: RT_GRP_LIGHTS_IN): every light's
+                             * sample rectangle lies inside the shrunk shell box, so a shadow ray from a point inside it cannot
+                             * be accepted by a shell triangle; skipped when that holds for every lane here */
+                            uint32_t skipS = 0u;
+                            if (shellSkip) {
+                                const float *SB = sm + lay.group + RT_GRP_SHELL_BOX;
+                                const bool in = (fabsf(P.x - SB[0]) < SB[4]) & (fabsf(P.y - SB[1]) < SB[5]) & (fabsf(P.z - SB[2]) < SB[6]);
+                                skipS = __reduce_and_sync(__activemask(), in ? shellSkip : 0u);
+                            }
                             if (withC && n >= 3u) {
-                                hitC = multi_hit<RT_MULTI_UNROLL, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd);                          /* :49 + :79-88 */
+                                hitC = multi_hit<RT_MULTI_UNROLL, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd, skipS);                   /* :49 + :79-88 */
                             } else if (withC) {
                                 hitC = dual_hit<false, UNROLL>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir[0], 0.0f, ltmax[0], shd[0]);
                                 if (n == 2u) shd[1] = any_hit<false, UNROLL>(sc, P, ldir[1], 0.0f, ltmax[1]);
                             } else if (n == 4u) {
-                                any_hit_multi<false, RT_MULTI_UNROLL, 4>(sc, P, ldir, ltmax, shd);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 4>(sc, P, ldir, ltmax, shd, skipS);
                             } else if (n == 3u) {
                                 f3 d3[3] = { ldir[0], ldir[1], ldir[2] }; float t3[3] = { ltmax[0], ltmax[1], ltmax[2] }; bool s3[3];
-                                any_hit_multi<false, RT_MULTI_UNROLL, 3>(sc, P, d3, t3, s3);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 3>(sc, P, d3, t3, s3, skipS);
                                 shd[0] = s3[0]; shd[1] = s3[1]; shd[2] = s3[2];
                             } else if (n == 2u) {
                                 f3 d2[2] = { ldir[0], ldir[1] }; float t2[2] = { ltmax[0], ltmax[1] }; bool s2[2];
-                                any_hit_multi<false, RT_MULTI_UNROLL, 2>(sc, P, d2, t2, s2);
+                                any_hit_multi<false, RT_MULTI_UNROLL, 2>(sc, P, d2, t2, s2, skipS);
                                 shd[0] = s2[0]; shd[1] = s2[1];
                             } else {
                                 shd[0] = any_hit<false, UNROLL>(sc, P, ldir[0], 0.0f, ltmax[0]);

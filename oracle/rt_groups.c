@@ -25,12 +25,14 @@
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_FACES (RT_GRP_SHELL_BOX + 8)
 #define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)
+#define RT_GRP_LIGHTS_IN (RT_GRP_FACES + 7)
 #define RT_GROUP_WORDS (RT_GRP_FACES + 8)
 
 extern void (*rt_oracle_query_hook)(const float o[3], const float d[3], float tmin, float tmax, int any,
                                     int hit, float distance, uint32_t primitive_id);
 extern _Thread_local float rt_oracle_light_sample[3];     /* rt_oracle.c: the sample point the shadow ray aims at */
 
+static int g_scene_has_spheres = 0;              /* rt_oracle_groups_spheres: the triangles of a scene with spheres are grouped for the shell's sake only */
 static const int g_light_normals_bound = 0;      /* (the library builds no groups' mask when a light-normal table is bound; the checker never binds one here) */
 int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L,
                      uint32_t out[RT_GROUP_WORDS]) {
@@ -126,7 +128,18 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
         for (uint32_t p = 0; p < P; p++)
             if (lo[p][1] == cy && hi[p][1] == cy) out[RT_GRP_LIGHT_PLANE] |= 1u << p;
     }
-    out[0] = K; out[1] = always; out[2] = K >= 1 ? 1u : 0u; out[3] = shell;
+    /* does every light's sample rectangle lie inside the shrunk shell box?  (rt_scene_layout.h: RT_GRP_LIGHTS_IN) */
+    {
+        const float *bx = (const float *)out + RT_GRP_SHELL_BOX;
+        int in = shell != 0 && !g_light_normals_bound;
+        for (uint32_t l = 0; l < L; l++) {
+            const float *c = (const float *)&lights[l];
+            const float hx = fmaxf(0.25f, 0.5f * c[12]), hz = fmaxf(0.25f, 0.5f * c[13]);
+            in = in && fabsf(c[0] - bx[0]) + hx < bx[4] && fabsf(c[1] - bx[1]) < bx[5] && fabsf(c[2] - bx[2]) + hz < bx[6];
+        }
+        out[RT_GRP_LIGHTS_IN] = in ? 1u : 0u;
+    }
+    out[0] = K; out[1] = always; out[2] = (K >= 1 && !g_scene_has_spheres) ? 1u : 0u; out[3] = shell;
     return (int)K;
 }
 
@@ -313,5 +326,56 @@ int rt_oracle_cullcheck_modeb(const CameraGPU *cameras, const MaterialGPU *mater
     rt_oracle_modeb_query_hook = 0;
     stats[0] = g_b.queries; stats[1] = g_b.mismatches; stats[2] = g_b.culledTests; stats[3] = g_b.fullTests;
     stats[4] = g_b.segQueries; stats[5] = g_b.segInShell;
+    return rc;
+}
+
+
+/* ---- the shell rule of the several-lights passes (csrc/wave.cuh: skipS), scenes with spheres included ----
+ * Every shadow query of a frame whose origin lies inside the shrunk shell box is repeated WITHOUT the shell triangles
+ * (all other triangles, then all spheres, the full loop's order): same answer required. */
+int rt_oracle_groups_spheres(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L, uint32_t out[RT_GROUP_WORDS]) {
+    g_scene_has_spheres = 1;
+    int K = rt_oracle_groups(vertices, T, lights, L, out);
+    g_scene_has_spheres = 0;
+    return K;
+}
+static struct { const float *spheres; uint32_t S; uint64_t shadow, skipped, mismatches; } g_sh;
+static void shell_hook(const float o[3], const float d[3], float tmin, float tmax, int any,
+                       int hit, float distance, uint32_t primitive_id) {
+    (void)distance; (void)primitive_id;
+    if (!any) return;
+    const float *bx = (const float *)g_chk.words + RT_GRP_SHELL_BOX;
+    int in = g_chk.words[RT_GRP_LIGHTS_IN] != 0;
+    for (int k = 0; k < 3; k++) in = in && fabsf(o[k] - bx[k]) < bx[4 + k];
+    int h = 0;
+    if (in) {
+        float bestN = tmax, bestD = 1.0f;
+        for (uint32_t i = 0; i < g_chk.T && !h; i++) {
+            if ((g_chk.words[3] >> (i / 2)) & 1u) continue;
+            const float *v = g_chk.vertices + (size_t)i * 12;
+            h = rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &bestN, &bestD);
+        }
+        for (uint32_t j = 0; j < g_sh.S && !h; j++) {
+            const float *sp = g_sh.spheres + (size_t)j * 20;
+            h = rt_sphere_test(sp, sp[16], o, d, tmin, &bestN, &bestD);
+        }
+    }
+#pragma omp critical
+    { g_sh.shadow++; g_sh.skipped += in; g_sh.mismatches += in && h != hit; }
+}
+/* stats: shadow queries, of those traced without the shell triangles, mismatches (must be 0) */
+int rt_oracle_shellcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                         const simd_float3 *vertices, const SphereGPU *spheres, const uint32_t *offsets, float *out,
+                         const RTLaunchParams *params, uint64_t stats[3], int nthreads) {
+    memset(&g_chk, 0, sizeof g_chk); memset(&g_sh, 0, sizeof g_sh);
+    if (params->numSpheres) rt_oracle_groups_spheres(vertices, params->numTriangles, lights, params->numLights, g_chk.words);
+    else rt_oracle_groups(vertices, params->numTriangles, lights, params->numLights, g_chk.words);
+    g_chk.vertices = (const float *)vertices; g_chk.T = params->numTriangles;
+    g_sh.spheres = (const float *)spheres; g_sh.S = params->numSpheres;
+    rt_oracle_query_hook = shell_hook;
+    uint64_t cnt[RT_CNT_COUNT];
+    int rc = rt_oracle_pathtrace(cameras, materials, lights, vertices, spheres, offsets, out, params, cnt, nthreads);
+    rt_oracle_query_hook = 0;
+    stats[0] = g_sh.shadow; stats[1] = g_sh.skipped; stats[2] = g_sh.mismatches;
     return rc;
 }

@@ -119,6 +119,14 @@ int  rt_oracle_sgridcheck(const CameraGPU *cameras, const MaterialGPU *materials
                           const simd_float3 *vertices, const SphereGPU *spheres, const uint32_t *offsets, float *out,
                           const RTLaunchParams *params, uint64_t stats[5], float firstBad[8], int nthreads);
 
+/* the group section of a scene WITH spheres (its triangles are grouped for the shell's sake only: word [2] stays 0), and the
+ * check of the several-lights passes' shell rule (csrc/wave.cuh): stats = shadow queries, of those repeated without the
+ * shell triangles, mismatches (must be 0) */
+int  rt_oracle_groups_spheres(const simd_float3 *vertices, uint32_t T, const SquareLightGPU *lights, uint32_t L, uint32_t out[52]);
+int  rt_oracle_shellcheck(const CameraGPU *cameras, const MaterialGPU *materials, const SquareLightGPU *lights,
+                          const simd_float3 *vertices, const SphereGPU *spheres, const uint32_t *offsets, float *out,
+                          const RTLaunchParams *params, uint64_t stats[3], int nthreads);
+
 int  rt_oracle_max_threads(void);
 
 #ifdef __cplusplus

@@ -120,6 +120,23 @@ def cullcheck_modeb(scene, width, height, *, camera_rays=6, mis_samples=300, nth
                 seg_queries=int(stats[4]), seg_in_shell=int(stats[5]), text=text, pixels=pixels)
 
 
+def shellcheck(scene, width, height, spp, *, bounces=3, seed=1, nthreads=0):
+    """Traces the frame; every shadow query from inside the shrunk shell box is repeated without the shell triangles
+    (oracle/rt_groups.c: the several-lights passes' shell rule).  Returns dict(shadow, skipped, mismatches, groups)."""
+    off = offsets(width, 0, height, seed)
+    out = np.zeros((height, width, 4), np.float32)
+    stats = np.zeros(3, np.uint64)
+    p = RTLaunchParams(width, height, 0, height, spp, 0, bounces, 0, scene["T"], scene["S"], scene["L"], 6, 300, 0, 0, 0)
+    rc = lib.rt_oracle_shellcheck(vp(scene["camera"]), vp(scene["materials"]), vp(scene["lights"]), vp(scene["vertices"]),
+                                  vp(scene["spheres"]), vp(off), vp(out), C.byref(p), vp(stats), nthreads)
+    if rc != 0:
+        raise RuntimeError(f"rt_oracle_shellcheck returned {rc}")
+    grp = np.zeros(52, np.uint32)
+    (lib.rt_oracle_groups_spheres if scene["S"] else lib.rt_oracle_groups)(vp(scene["vertices"]), C.c_uint32(scene["T"]), vp(scene["lights"]),
+                                                                           C.c_uint32(scene["L"]), vp(grp))
+    return dict(shadow=int(stats[0]), skipped=int(stats[1]), mismatches=int(stats[2]), groups=grp, image=out)
+
+
 def sgridcheck(scene, width, height, spp, *, bounces=3, seed=1, y0=0, y1=None, nthreads=0):
     """Traces rows [y0, y1) of the frame; the sphere part of every ray query is repeated by walking the sphere grid
     (oracle/rt_sgrid.c).  Returns dict(queries, mismatches, cells, tests, ok, first_bad[8], image)."""

@@ -154,3 +154,21 @@ def test_exit_and_light_plane_rules_in_other_rooms():
                 c[0:3] = cam; c[4:7] = (0.1, -0.1, -1.0); c[14] = 1.4
             r = O.cullcheck(sc, W, H, spp, bounces=4)
             assert r["queries"] > 250_000 and r["mismatches"] == 0, (mode, cam, r["mismatches"])
+
+
+def test_shell_rule_of_the_several_lights_passes_sphere_scene():
+    """csrc/wave.cuh skips the shell triangles (the walls) for all shadow rays of a pass when every light's sample rectangle and
+    every lane's shading point lie inside the shrunk shell box -- on config 4's scene too, whose triangles are grouped for
+    the shell's sake only.  Every shadow query of a frame from inside the box, repeated without the walls but with all spheres."""
+    W, H = 320, 180
+    sc = O.spheres(W, H)
+    r = O.shellcheck(sc, W, H, 4)
+    g = r["groups"]
+    assert int(g[2]) == 0 and int(g[3]) == 0b11111 and int(g[51]) == 1           # not for the sorted kernels; five walls; lights inside
+    assert r["shadow"] > 1_500_000 and r["skipped"] > 0.999 * r["shadow"] and r["mismatches"] == 0
+    assert np.array_equal(r["image"], O.pathtrace(sc, W, H, 4)[0])
+    # a light that reaches out of the box switches the rule off (the word, not the geometry, decides)
+    sc["lights"].view(np.float32)[0] = 2.4
+    assert int(O.shellcheck(sc, 64, 36, 1)["groups"][51]) == 0
+    # the Cornell scene: one light, inside
+    assert int(O.groups(O.cornell(64, 64))[51]) == 1
