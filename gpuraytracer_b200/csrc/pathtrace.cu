@@ -168,10 +168,11 @@ __device__ void prep_groups(const unsigned char *__restrict__ vertices, const un
         const uint32_t hiFace = __ballot_sync(0xffffffffu, face && lo[k] == hi[k] && lo[k] == ahi[k]);
         if (lane == 0) { gu[RT_GRP_FACES + 2 * k] = loFace; gu[RT_GRP_FACES + 2 * k + 1] = hiFace; }
     }
-    /* the quads in the plane of the one light (rt_scene_layout.h: RT_GRP_LIGHT_PLANE) */
+    /* the quads in the plane of the light(s) (rt_scene_layout.h: RT_GRP_LIGHT_PLANE) */
     {
         const float cy = ((const float *)lights)[1];
-        const bool ok1 = lay.L == 1u && !(lay.flags & RT_LAYOUT_LIGHT_NORMALS) && ext < 64.0f;
+        bool ok1 = lay.L >= 1u && !(lay.flags & RT_LAYOUT_LIGHT_NORMALS) && ext < 64.0f;
+        for (uint32_t l = 1; l < lay.L; l++) ok1 = ok1 && ((const float *)(lights + 64 * (size_t)l))[1] == cy;     /* several lights: in ONE plane */
         const uint32_t inPlane = __ballot_sync(0xffffffffu, has && ok1 && lo[1] == cy && hi[1] == cy);
         if (lane == 0) gu[RT_GRP_LIGHT_PLANE] = inPlane;
     }

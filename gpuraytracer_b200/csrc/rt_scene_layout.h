@@ -36,7 +36,7 @@
  *            quad's face plane ahead of it, and only if the crossing point lies within the face grown by the margin; so
  *            the ray is tested against the shell quads of the faces it can leave the box through -- one, as a rule --
  *            instead of all of them (sortedblk.cuh: part of the sort key).
- *            RT_GRP_LIGHT_PLANE: with ONE light, normal (0,-1,0), the quads whose six vertices have the light centre's y,
+ *            RT_GRP_LIGHT_PLANE: with one light (or several whose centres share one y), normal (0,-1,0), the quads whose six vertices have the light centre's y,
  *            bit for bit -- the light's own geometry.  Every light sample point has that y too, so a shadow ray crosses
  *            the plane AT its sample point, at t = ldist up to 1e-6 x ldist, and the shadow test ends at ldist - 1e-3
  *            (raytrace.metal:81): such a quad cannot be accepted by any shadow ray of the scene and is left out of their
@@ -110,7 +110,7 @@
 #define RT_GRP_SHELL      3
 #define RT_GRP_SHELL_BOX (4 + 8 * RT_MAX_GROUPS)
 #define RT_GRP_FACES     (RT_GRP_SHELL_BOX + 8)     /* 6 pair masks: the shell quads in face 2 * axis + (1 = high side) */
-#define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)      /* pair mask: quads in the plane of the (one) light */
+#define RT_GRP_LIGHT_PLANE (RT_GRP_FACES + 6)      /* pair mask: quads in the plane of the light(s) */
 #define RT_GRP_LIGHTS_IN   (RT_GRP_FACES + 7)      /* 1: the sample rectangle of EVERY light lies inside the shrunk shell box */
 #define RT_GROUP_WORDS   (RT_GRP_FACES + 8)
 

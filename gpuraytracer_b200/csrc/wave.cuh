@@ -138,6 +138,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
     const uint32_t nb = (uint32_t)p.bounces, numLights = p.numLights;
     const bool paired = ((const uint32_t *)sm)[RT_HDR_PAIRED] != 0u;           /* quads cut in two: pathtrace.cu, PAIRED */
     /* the shell quads the shadow rays of a several-lights pass may skip (0: none, or some light reaches out of the shell box) */
+    const uint32_t lightPlane = ((const uint32_t *)sm)[lay.group + RT_GRP_LIGHT_PLANE];
     const uint32_t shellSkip = ((const uint32_t *)sm)[lay.group + RT_GRP_LIGHTS_IN] ? ((const uint32_t *)sm)[lay.group + RT_GRP_SHELL] : 0u;
     Counters cnt = { 0u, 0u, 0u };
     unsigned long long paths = 0ull;
@@ -375,6 +376,7 @@ __device__ __forceinline__ void pathtrace_wave_body(const float *__restrict__ sc
                                 const bool in = (fabsf(P.x - SB[0]) < SB[4]) & (fabsf(P.y - SB[1]) < SB[5]) & (fabsf(P.z - SB[2]) < SB[6]);
                                 skipS = __reduce_and_sync(__activemask(), in ? shellSkip : 0u);
                             }
+                            skipS |= lightPlane;            /* the lights' own quads: no shadow ray reaches them before its end (RT_GRP_LIGHT_PLANE) */
                             if (withC && n >= 3u) {
                                 hitC = multi_hit<RT_MULTI_UNROLL, 4>(sc, P, rd, 0.001f, 1000.0f, dist, id, ldir, ltmax, shd, skipS);                   /* :49 + :79-88 */
                             } else if (withC) {

@@ -123,7 +123,9 @@ int rt_oracle_groups(const simd_float3 *vertices, uint32_t T, const SquareLightG
                     }
     }
     /* the quads in the plane of the one light: no shadow ray can be accepted by them (rt_scene_layout.h) */
-    if (L == 1 && ext < 64.0f && !g_light_normals_bound) {
+    int onePlane = L >= 1 && ext < 64.0f && !g_light_normals_bound;
+    for (uint32_t l = 1; l < L; l++) onePlane = onePlane && ((const float *)&lights[l].center)[1] == ((const float *)&lights[0].center)[1];
+    if (onePlane) {
         const float cy = ((const float *)&lights[0].center)[1];
         for (uint32_t p = 0; p < P; p++)
             if (lo[p][1] == cy && hi[p][1] == cy) out[RT_GRP_LIGHT_PLANE] |= 1u << p;
@@ -348,10 +350,12 @@ static void shell_hook(const float o[3], const float d[3], float tmin, float tma
     int in = g_chk.words[RT_GRP_LIGHTS_IN] != 0;
     for (int k = 0; k < 3; k++) in = in && fabsf(o[k] - bx[k]) < bx[4 + k];
     int h = 0;
+    const uint32_t skip = (in ? g_chk.words[3] : 0u) | g_chk.words[RT_GRP_LIGHT_PLANE];     /* the quads in the lights' plane: from anywhere */
+    in = skip != 0;
     if (in) {
         float bestN = tmax, bestD = 1.0f;
         for (uint32_t i = 0; i < g_chk.T && !h; i++) {
-            if ((g_chk.words[3] >> (i / 2)) & 1u) continue;
+            if ((skip >> (i / 2)) & 1u) continue;
             const float *v = g_chk.vertices + (size_t)i * 12;
             h = rt_triangle_test(v, v + 4, v + 8, o, d, tmin, &bestN, &bestD);
         }
