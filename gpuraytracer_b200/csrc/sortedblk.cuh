@@ -18,6 +18,9 @@
 #ifndef RT_EXP_SORT_UNROLL
 #define RT_EXP_SORT_UNROLL 2   /* A/B (profiles/r04x_ab.log: 1: 55.54 ms, 2: 55.09, 3: 55.35 at 256 spp): iterations of the rank loop in flight (a chain of dependent shared-memory round trips each) */
 #endif
+#ifndef RT_EXP_RANK_IN_A
+#define RT_EXP_RANK_IN_A 1     /* A/B: 1 = an entry's rank within its key is taken in pass A (the sort loses its match and its atomic, gains a barrier) */
+#endif
 #ifndef RT_EXP_TICKET_AHEAD
 #define RT_EXP_TICKET_AHEAD 1  /* A/B (tools/build_exp.sh): 1 = pass B draws the next chunk's ticket before tracing the current chunk */
 #endif
@@ -353,7 +356,17 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                 }
                 if (sort) {
                     const uint32_t same = __match_any_sync(0xffffffffu, key);
-                    if (active && lane == (uint32_t)__ffs((int)same) - 1u) atomicAdd(&cnts[key], (uint32_t)__popc(same));
+                    if (RT_EXP_RANK_IN_A) {
+                        /* the entry's rank within its key comes back from the counter it is counted in (kept in the sorted
+                         * list's own storage until the sort turns rank into place) */
+                        const uint32_t leader = (uint32_t)__ffs((int)same) - 1u;
+                        uint32_t at = 0u;
+                        if (active && lane == leader) at = atomicAdd(&cnts[key], (uint32_t)__popc(same));
+                        at = __shfl_sync(0xffffffffu, at, leader);
+                        if (active) sorted[e] = (uint16_t)(at + __popc(same & lt));
+                    } else {
+                        if (active && lane == (uint32_t)__ffs((int)same) - 1u) atomicAdd(&cnts[key], (uint32_t)__popc(same));
+                    }
                 }
             }
             __syncthreads();
@@ -379,6 +392,25 @@ __device__ __forceinline__ void pathtrace_sortedblk_body(const float *__restrict
                     for (uint32_t q = 0; q < PER; q++) { if (lane * PER + q < NK) startOf[NK - 1u - (lane * PER + q)] = at; at += c[q]; }
                     __syncwarp();
                 }
+                if (RT_EXP_RANK_IN_A) {
+                    /* every entry's place = start of its key + its rank: all read (a thread has at most NSLOT / 128 entries),
+                     * then, behind a barrier, all written -- ranks and places share the sorted list's storage */
+                    constexpr uint32_t PT = NSLOT / RT_BLOCK_THREADS;
+                    uint32_t place[PT];
+#pragma unroll
+                    for (uint32_t q = 0; q < PT; q++) {
+                        const uint32_t e = warp * 32u + lane + q * RT_BLOCK_THREADS;
+                        place[q] = 0xffffffffu;
+                        if (e < count) {
+                            const uint32_t slot = hitlist[e];
+                            place[q] = ((startOf[SL.key(slot) & (NK - 1u)] + sorted[e]) << 16) | slot;
+                        }
+                    }
+                    __syncthreads();
+#pragma unroll
+                    for (uint32_t q = 0; q < PT; q++)
+                        if (place[q] != 0xffffffffu) sorted[place[q] >> 16] = (uint16_t)(place[q] & 0xffffu);
+                } else
 #pragma unroll SORT_UNROLL
                 for (uint32_t c0 = warp * 32u; c0 < count; c0 += RT_BLOCK_THREADS) {
                     const uint32_t e = c0 + lane;
