@@ -17,7 +17,8 @@ cap a pathTrace python bench.py --steps 1 --warmup 3 --spp 64 --no-cpu-baseline
 python tools/ncu_constants.py /tmp/rep/a.ncu-rep 1920 1080 64 profiles/${TAG}_a_ncu_full_summary.txt > $O/${TAG}_ncu_constants.json
 B=$(cuobjdump -sass -fun pathTrace_sortedblk6 gpuraytracer_b200/csrc/build/pathtrace.cubin | grep BAR.SYNC | sed 's/.*\/\*\([0-9a-f]*\)\*\/.*/0x\1/' | tr '\n' ' ')
 set -- $B; echo "barriers: $B" > $O/${TAG}_regions.txt
-python tools/ncu_regions.py /tmp/rep/a.ncu-rep 0x0:$2:stage $2:$3:camera $3:$4:passA $4:$5:sort $5:$6:passB $6:$7:accum >> $O/${TAG}_regions.txt
+# barriers of the entry: staging | tables | camera | pass A | sort (read ranks | write places) | pass B | (fallback body follows)
+python tools/ncu_regions.py /tmp/rep/a.ncu-rep 0x0:$2:stage $2:$3:camera $3:$4:passA $4:$6:sort $6:$7:passB $7:$8:accum >> $O/${TAG}_regions.txt
 cap c pathTrace python bench.py --config 4 --steps 1 --warmup 3 --spp 32 --no-cpu-baseline
 cap modeb drawTriangle python bench.py --config modeb --steps 1 --warmup 3 --no-cpu-baseline
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
