@@ -10,8 +10,13 @@
  * camera phase and the in-order accumulation (raytrace.metal:103) are each warp's own; in between, any warp may
  * trace any path.  Same arithmetic, same bits.
  *
- * Price: block barriers (camera | per bounce: A | rank | B) instead of __syncwarp, shared-memory atomics for the
+ * Price: block barriers (camera | per bounce: A | sort, twice | B) instead of __syncwarp, shared-memory atomics for the
  * key counters and list appends.
+ *
+ * Since round 2 the key also says through which face of the room the continuation ray can leave it (the exit rule,
+ * rt_scene_layout.h: three more bits, 128 keys; not in the wide form), the shadow rays skip the walls (shell rule) and
+ * the light's own quads (light-plane rule), and an entry's rank within its key is the value pass A's counter returns, so
+ * that the sort only turns ranks into places: 5.0 quads per step for the continuation ray, 80 warp instructions a path.
  */
 #pragma once
 
