@@ -47,3 +47,20 @@ def test_other_sphere_counts_and_a_crowded_cell(dev):
     r = G.Renderer(gsc, W, H, device=dev)
     for variant in (L.VARIANT_SMEM, L.VARIANT_WAVE, L.VARIANT_DEFAULT):
         assert np.array_equal(r.draw(spp=4, variant=variant), ref), variant
+
+
+def test_random_sphere_scenes(dev):
+    """Spheres thrown at random into config 4's room (tests/test_sgrid_cpu.py: random_sphere_scene -- radii from 0.02 to 0.9,
+    some through a wall, every tenth on its neighbour's centre; the crowded scenes overflow a cell and fall back to the full
+    loop on the device as they do in the checker): every form against the oracle, four bounces."""
+    from test_sgrid_cpu import random_sphere_scene
+    W, H = 120, 68
+    for seed, n in ((1, 1), (2, 7), (3, 40), (4, 40), (5, 120), (6, 256), (7, 256), (8, 19)):
+        osc = random_sphere_scene(W, H, seed, n)
+        gsc = G.init_sphere_scene(W, H, num_spheres=n)
+        gsc.spheres[:] = osc["spheres"].view(np.uint8)
+        ref, _ = O.pathtrace(osc, W, H, 4, bounces=4)
+        r = G.Renderer(gsc, W, H, device=dev)
+        for variant in (L.VARIANT_SMEM, L.VARIANT_DEFAULT, L.VARIANT_WAVE, L.VARIANT_TILES):
+            img = r.draw(spp=4, bounces=4, variant=variant)
+            assert np.array_equal(img, ref), (seed, n, variant, int((img != ref).any(axis=2).sum()))

@@ -41,3 +41,28 @@ def test_grid_other_sphere_counts_and_overflow():
     sph[:12, 0:3] = sph[0, 0:3]                             # twelve spheres on one spot
     r = O.sgridcheck(sc, W, H, 1)
     assert not r["ok"] and r["queries"] == 0
+
+
+def random_sphere_scene(W, H, seed, n):
+    """Config 4's room and lights with `n` spheres thrown at random: centres anywhere in the room (some poke through a wall),
+    radii log-uniform from 0.02 to 0.9 (a few span several cells of the grid, some cells overflow for large n), every tenth
+    sphere a copy of its neighbour's centre (equal distances: the tie rule)."""
+    sc = O.spheres(W, H, n=n)
+    g = np.random.default_rng(seed)
+    s = sc["spheres"].view(np.float32).reshape(-1, 20)
+    s[:, 0:3] = g.uniform(-2.4, 2.4, (n, 3)).astype(np.float32)
+    s[:, 16] = np.exp(g.uniform(np.log(0.02), np.log(0.9), n)).astype(np.float32)
+    for j in range(9, n, 10):
+        s[j, 0:3] = s[j - 1, 0:3]
+    return sc
+
+
+def test_grid_never_changes_a_query_random_sphere_scenes():
+    W, H = 120, 68
+    usable = total = 0
+    for seed, n in ((1, 1), (2, 7), (3, 40), (4, 40), (5, 120), (6, 256), (7, 256), (8, 19)):
+        sc = random_sphere_scene(W, H, seed, n)
+        r = O.sgridcheck(sc, W, H, 4, bounces=4)
+        assert r["mismatches"] == 0, (seed, n, r["mismatches"], r["first_bad"])
+        usable += r["ok"]; total += r["queries"]
+    assert usable >= 5 and total > 500_000          # the crowded ones overflow a cell and are traced by the full loop instead
