@@ -49,3 +49,16 @@ def test_modeb_parameters_and_row_tile():
     w2p, w2t, _ = O.drawtriangle(O.cornell(W, H, 1.5), W, H, row0=4, rows=8, camera_rays=2, mis_samples=30,
                                  tile_rows=4, tile_stride=8)
     check(tx2, px2, w2t, w2p)
+
+
+def test_modeb_group_and_shell_rule_other_scenes():
+    """closest_b's group rule over a warp's union and its shell rule (origins 1e-4 off their surface) away from the Cornell
+    box: tests/test_group_cull_cpu.py: modeb_scenes -- the CPU checker's side of the same scenes."""
+    from test_group_cull_cpu import modeb_scenes
+    W, H = 64, 48
+    for name, osc in modeb_scenes(W, H):
+        gsc = G.init_cornell_box(W, H, light_size=1.5)
+        gsc.vertices[:] = osc["vertices"].view(np.uint8); gsc.lights[:] = osc["lights"].view(np.uint8); gsc.camera[:] = osc["camera"].view(np.uint8)
+        px, tx = G.draw_triangle(gsc, W, H, camera_rays=2, mis_samples=30)
+        want_px, want_tx, _ = O.drawtriangle(osc, W, H, camera_rays=2, mis_samples=30)
+        assert np.array_equal(tx.view(np.uint32), want_tx.view(np.uint32)), (name, int((tx != want_tx).sum()))

@@ -172,3 +172,31 @@ def test_shell_rule_of_the_several_lights_passes_sphere_scene():
     assert int(O.shellcheck(sc, 64, 36, 1)["groups"][51]) == 0
     # the Cornell scene: one light, inside
     assert int(O.groups(O.cornell(64, 64))[51]) == 1
+
+
+def modeb_scenes(W, H):
+    """Scenes for mode B's group / shell rule away from the Cornell box: the two rooms of other_room, and four seeded scenes
+    whose boxes have random size, place, yaw and tilt (some through a wall), each with a camera inside the room."""
+    out = []
+    for mode in ("stretched", "flush"):
+        out.append((mode, other_room(W, H, mode)))
+    g = np.random.default_rng(23)
+    for k in range(4):
+        sc = O.cornell(W, H, light_size=1.5)
+        f = sc["vertices"].view(np.float32)
+        for t0 in (10, 22):
+            _box(f, t0, g.uniform(-2.3, 2.3, 3), g.uniform(0.05, 1.1, 3) + 0.02, g.uniform(0, np.pi), g.uniform(-0.6, 0.6) * (k % 2))
+        cam = sc["camera"].view(np.float32)
+        cam[0:3] = g.uniform(-1.5, 1.5, 3) + (0, 0, 1.0); cam[4:7] = g.uniform(-0.4, 0.4, 3) + (0, 0, -1.0); cam[14] = g.uniform(0.8, 1.6)
+        out.append((f"boxes{k}", sc))
+    return out
+
+
+def test_culling_never_changes_a_query_modeb_other_scenes():
+    W, H = 64, 48
+    total = 0
+    for name, sc in modeb_scenes(W, H):
+        r = O.cullcheck_modeb(sc, W, H, camera_rays=2, mis_samples=30)
+        assert r["mismatches"] == 0, (name, r["mismatches"])
+        total += r["queries"]
+    assert total > 800_000
