@@ -64,3 +64,23 @@ def test_random_sphere_scenes(dev):
         for variant in (L.VARIANT_SMEM, L.VARIANT_DEFAULT, L.VARIANT_WAVE, L.VARIANT_TILES):
             img = r.draw(spp=4, bounces=4, variant=variant)
             assert np.array_equal(img, ref), (seed, n, variant, int((img != ref).any(axis=2).sum()))
+
+
+def test_lights_off_the_common_plane_or_out_of_the_shell_box(dev):
+    """The several-lights passes drop the walls and the lights' own quads from their shadow rays only when rt_prep_scene says
+    they may (RT_GRP_LIGHTS_IN, RT_GRP_LIGHT_PLANE).  A light lowered out of the others' plane, a light whose sample
+    rectangle reaches through the wall, both: the rules switch off piecewise and the image stays the oracle's."""
+    W, H = 160, 90
+    for case in ("lowered", "through_wall", "both"):
+        osc = O.spheres(W, H, n=64); gsc = G.init_sphere_scene(W, H, num_spheres=64)
+        for lights in (osc["lights"].view(np.float32), gsc.lights.view(np.float32)):
+            if case in ("lowered", "both"):
+                lights[1] = 2.0                     # light 0: centre.y
+            if case in ("through_wall", "both"):
+                lights[16 + 0] = 2.4                # light 1: centre.x, 0.1 from the wall, half extent 0.25
+        g = O.shellcheck(osc, 32, 18, 1)["groups"]
+        assert int(g[50]) == (0 if case != "through_wall" else 0b111100000) and int(g[51]) == (1 if case == "lowered" else 0)
+        ref, _ = O.pathtrace(osc, W, H, 4)
+        r = G.Renderer(gsc, W, H, device=dev)
+        for variant in (L.VARIANT_SMEM, L.VARIANT_DEFAULT, L.VARIANT_WAVE):
+            assert np.array_equal(r.draw(spp=4, variant=variant), ref), (case, variant)
